@@ -1,0 +1,227 @@
+/*
+ * pygb.h — C ABI of libpygb.so: B200 (sm_100a) kernels for the message-passing
+ * hot path of ggzhang0071/pytorch_geometric-1.
+ *
+ * What this boundary replaces.  The reference reaches native code for this
+ * path only through the pinned packages torch-scatter==2.0.4
+ * (/root/reference/requirement.txt:3) and torch-geometric==1.4.3
+ * (requirement.txt:7): `torch.ops.torch_scatter.scatter_{sum,mean,max}(src,
+ * index, dim, out, dim_size)` plus ATen `index_select`/`matmul`, called from
+ * `MessagePassing.propagate` (reference call sites: gmm_conv.py:131,
+ * README.md:43, examples/gcn.py:25,27, ConvexPruning.py:196,221).  Each entry
+ * point below names the reference interface it stands in for (SURVEY.md
+ * Appendix A section + in-tree call site).
+ *
+ * Conventions
+ *  - extern "C"; plain pointers and sizes; no torch / C++ types.
+ *  - Every pointer is a DEVICE pointer owned by the caller (torch's caching
+ *    allocator on the Python side).  The library never allocates or frees
+ *    device memory and never synchronises the stream; scratch space is passed
+ *    in as `ws` with the size reported by the matching *_workspace() call.
+ *  - Every call takes the CUDA stream to launch on (cudaStream_t passed as
+ *    void*), is re-entrant, and returns 0 on success or a negative PYGB_E_*
+ *    code; pygb_last_error() returns the thread-local message.
+ *  - Index arrays coming from the reference API (`edge_index`, `index`) are
+ *    int64 as in PyG; the compact CSR the kernels consume is int32
+ *    (E', N < 2^31).
+ *  - dtype: PYGB_F32 or PYGB_BF16 for feature matrices; accumulation is
+ *    always fp32.
+ */
+#ifndef PYGB_H_
+#define PYGB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PYGB_ABI_VERSION 1
+
+enum { PYGB_OK = 0, PYGB_E_ARG = -1, PYGB_E_CUDA = -2, PYGB_E_WORKSPACE = -3,
+       PYGB_E_UNSUPPORTED = -4 };
+enum { PYGB_F32 = 0, PYGB_BF16 = 1 };
+enum { PYGB_SUM = 0, PYGB_MEAN = 1 };
+/* self-loop handling, SURVEY A.2 */
+enum { PYGB_LOOPS_REMOVE = 0,        /* remove_self_loops                       */
+       PYGB_LOOPS_ADD = 1,           /* add_self_loops (keeps existing loops)   */
+       PYGB_LOOPS_REMOVE_ADD = 2,    /* GATConv.forward: remove then add        */
+       PYGB_LOOPS_ADD_REMAINING = 3  /* GCNConv.norm: add_remaining_self_loops  */ };
+
+typedef void* pygb_stream_t; /* cudaStream_t */
+
+int pygb_abi_version(void);
+const char* pygb_last_error(void);
+/* Fails (PYGB_E_UNSUPPORTED) unless the current device is compute capability 10.x. */
+int pygb_check_device(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- K4: graph build (integer outputs bit-exact vs the oracle) ------------ */
+
+/* Number of edges with row == col -> *d_count (device int64).  Replaces the
+ * `mask = row != col` + masked-select size sync of remove_self_loops /
+ * add_remaining_self_loops (A.2; ref site examples/qm9_nn_conv.py:11). */
+int pygb_count_self_loops(const int64_t* edge_index, int64_t E, int64_t* d_count,
+                          pygb_stream_t s);
+
+/* Self-loop handling (A.2).  `n_loops` is the value of pygb_count_self_loops
+ * (ignored for PYGB_LOOPS_ADD).  E' = E - n_loops (REMOVE), E + N (ADD),
+ * E - n_loops + N (REMOVE_ADD, ADD_REMAINING).  Output order: surviving edges
+ * in original order, then loops 0..N-1.  edge_weight/out_edge_weight may be
+ * NULL together.  ADD_REMAINING keeps an existing loop's weight; if a node has
+ * several, the one with the highest edge id wins (the CPU reference's
+ * last-write order, Q1). */
+size_t pygb_apply_loops_workspace(int64_t E, int64_t N);
+int pygb_apply_loops(const int64_t* edge_index, int64_t E, int64_t N, int mode,
+                     int64_t n_loops, const float* edge_weight, float fill_value,
+                     int64_t* out_edge_index, float* out_edge_weight, void* ws,
+                     size_t ws_bytes, pygb_stream_t s);
+
+/* Stable sort of E edges by key[e] in [0, n_rows): rowptr[n_rows+1],
+ * perm[E] = original edge ids grouped by key, ascending inside a group
+ * (so sequential reductions see the reference's CPU edge order), and, if
+ * `other` != NULL, col[p] = (int32) other[perm[p]].  This is the structure that
+ * replaces the per-element atomics of scatter_cuda.cu (A.4-A.6): all
+ * reductions below walk it without atomics.  Keys outside [0, n_rows) set
+ * *d_status (device int32, may be NULL) to 1 and are dropped from rowptr;
+ * `other` values outside [0, n_cols) set it to 2 and are stored as 0. */
+size_t pygb_csr_build_workspace(int64_t E, int64_t n_rows);
+int pygb_csr_build(const int64_t* key, const int64_t* other, int64_t E,
+                   int64_t n_rows, int64_t n_cols, int32_t* rowptr, int32_t* perm,
+                   int32_t* col, int32_t* d_status, void* ws, size_t ws_bytes,
+                   pygb_stream_t s);
+
+/* out[p] = src[perm[p]] for a float edge attribute (weights into CSR order). */
+int pygb_permute_f32(const float* src, const int32_t* perm, int64_t E, float* out,
+                     pygb_stream_t s);
+
+/* utils.degree (A.2; ref site examples/faust.py:19): counts per key as int64
+ * or float32 (out_is_float).  Exact (integer atomics). */
+int pygb_degree(const int64_t* index, int64_t E, int64_t N, int out_is_float,
+                void* out, pygb_stream_t s);
+
+/* deg[j] = sum_p w[perm[p]] over row j of a CSR keyed on the index to count
+ * (GCNConv.norm uses `row`, A.9 Q8), added sequentially in ascending edge id —
+ * the CPU reference's scatter_add_ order, hence bit-identical fp32 degrees. */
+int pygb_weighted_degree(const float* w, const int32_t* rowptr, const int32_t* perm,
+                         int64_t N, float* deg, pygb_stream_t s);
+
+/* GCNConv.norm (A.9; ref sites examples/gcn.py:18-19, ConvexPruning.py:180-185):
+ * dis = deg^-1/2 with inf -> 0, norm[e] = (dis[row[e]]*w[e])*dis[col[e]];
+ * `w` NULL means all ones.  edge_index is the loop-augmented [2,E'] array and
+ * deg comes from pygb_degree (unit weights) or pygb_weighted_degree. */
+int pygb_gcn_norm(const int64_t* edge_index, const float* w, int64_t E, int64_t N,
+                  const float* deg, float* norm, pygb_stream_t s);
+
+/* ---- K1: segmented gather-reduce (aggr = add | mean) ---------------------- */
+
+/* out[i, :] = reduce_{p in [rowptr[i], rowptr[i+1])} w_p * x[idx[p], :]
+ *   w_p = 1 if edge_w == NULL, edge_w[p] if wperm == NULL, else edge_w[wperm[p]].
+ *   reduce = PYGB_SUM or PYGB_MEAN (sum / max(count,1), A.5);  bias (fp32[F],
+ *   may be NULL) is added after the reduction (GCNConv.update).
+ * Fuses index_select + message (norm * x_j) + scatter_add of
+ * MessagePassing.propagate (A.1/A.4; ref sites examples/gcn.py:25,27).  With
+ * idx = perm it reduces a materialised [E,F] message tensor given in original
+ * edge order (the generic `scatter_` path, A.3).  One warp per row, 128-bit
+ * loads when x/out/ld* are 16-byte aligned, fixed summation order, no atomics.
+ * ldx/ldo are row strides in elements. */
+int pygb_seg_gather_reduce(int reduce, int dtype, const void* x, int64_t ldx,
+                           int64_t F, const int32_t* rowptr, const int32_t* idx,
+                           const float* edge_w, const int32_t* wperm,
+                           const float* bias, int64_t n_rows, void* out,
+                           int64_t ldo, pygb_stream_t s);
+
+/* Same walk with a per-(edge, head) weight: out[i,h,:] = sum_p
+ * head_w[wp(p)*H + h] * x[idx[p],h,:], wp(p) = wperm ? wperm[p] : p — GAT's
+ * `x_j * alpha.view(-1,H,1)` + scatter_add (A.10) and its transpose. */
+int pygb_seg_gather_reduce_heads(int dtype, const void* x, int64_t ldx, int H, int C,
+                                 const int32_t* rowptr, const int32_t* idx,
+                                 const float* head_w, const int32_t* wperm,
+                                 const float* bias, int64_t n_rows, void* out,
+                                 int64_t ldo, pygb_stream_t s);
+
+/* out[e, :] = x[index[e], :] — the x_i / x_j gathers of propagate for generic
+ * message() functions (A.1 step 2; ref site README.md:45-49). index is int64. */
+int pygb_gather_rows(int dtype, const void* x, int64_t ldx, int64_t F,
+                     const int64_t* index, int64_t E, void* out, int64_t ldo,
+                     pygb_stream_t s);
+
+/* ---- K3: segmented max with argmax (aggr = max) --------------------------- */
+
+/* out[i,f] = max_p src[idx[p], f] over row i, arg[i,f] = eid[p] of the FIRST
+ * maximal entry in ascending edge-id order (strict '>', NaN never wins; A.6
+ * Q4), rows without a winner: value 0, arg = E_fill (Q5).  Values below
+ * `zero_below` are then replaced by 0 (utils.scatter_'s `out[out < -10000] = 0`,
+ * A.3 Q2; pass -INFINITY to disable); with mask_arg != 0 their arg becomes
+ * E_fill too, which is what the autograd of that in-place overwrite needs.
+ * idx = eid = perm reduces a message tensor; idx = col, eid = perm is the fused
+ * gather-max.  arg may be NULL.
+ * Replaces scatter_kernel<max> + scatter_arg_kernel of scatter_cuda.cu. */
+int pygb_seg_max(int dtype, const void* src, int64_t lds, int64_t F,
+                 const int32_t* rowptr, const int32_t* idx, const int32_t* eid,
+                 int64_t n_rows, int64_t E_fill, float zero_below, int mask_arg,
+                 void* out, int64_t ldo, int64_t* arg, pygb_stream_t s);
+
+/* Backward of K3: grad_src[e,f] = grad_out[i,f] where arg[i,f] == e, else 0.
+ * grad_src must be zero-filled by the caller; one writer per element. */
+int pygb_seg_max_backward(const float* grad_out, int64_t ldg, const int64_t* arg,
+                          int64_t n_rows, int64_t F, int64_t E, float* grad_src,
+                          int64_t lds, pygb_stream_t s);
+
+/* ---- K2: edge softmax and fused GAT -------------------------------------- */
+
+/* utils.softmax (A.7): out[e,h] = exp(src[e,h] - max_row) /
+ * (sum_row exp(..) + 1e-16), rows given by rowptr/perm over `index`.  src/out
+ * are [E,H] fp32 in original edge order. */
+int pygb_edge_softmax(const float* src, int64_t H, const int32_t* rowptr,
+                      const int32_t* perm, int64_t n_rows, float* out,
+                      pygb_stream_t s);
+/* grad_src[e,h] = out[e,h] * (g[e,h] - sum_row(out*g)). */
+int pygb_edge_softmax_backward(const float* out, const float* grad_out, int64_t H,
+                               const int32_t* rowptr, const int32_t* perm,
+                               int64_t n_rows, float* grad_src, pygb_stream_t s);
+
+/* a_dst[n,h] = <xw[n,h,:], att[h,:C]>,  a_src[n,h] = <xw[n,h,:], att[h,C:]>
+ * (the two halves of GATConv.message's `(cat[x_i,x_j]*att).sum(-1)`, A.10).
+ * a_dst may be NULL. */
+int pygb_gat_scores(int dtype, const void* xw, int64_t ldx, const float* att,
+                    int64_t N, int H, int C, float* a_src, float* a_dst,
+                    pygb_stream_t s);
+
+/* Fused GATConv propagate (A.10; ref sites ConvexPruning.py:209-221,
+ * examples/ppi.py:22-28): for row i, head h
+ *   l_p = leaky_relu(a_dst[i,h] + a_src[col[p],h]);  m = max_p l_p
+ *   out[i,h,:] = sum_p exp(l_p - m) * xw[col[p],h,:] / (sum_p exp(l_p - m) + 1e-16)
+ * a_dst may be NULL (bipartite x_i = None).  row_max/row_sum [n_rows,H] are
+ * written for the backward (may be NULL).  bias fp32[H*C] may be NULL. */
+int pygb_gat_forward(int dtype, const void* xw, int64_t ldx, const float* a_src,
+                     const float* a_dst, int H, int C, float negative_slope,
+                     const int32_t* rowptr, const int32_t* col, int64_t n_rows,
+                     const float* bias, void* out, int64_t ldo, float* row_max,
+                     float* row_sum, pygb_stream_t s);
+
+/* alpha[e,h] of the fused forward, recomputed from the saved row statistics,
+ * written in ORIGINAL edge order (e = perm[p], or p if perm == NULL). */
+int pygb_gat_alpha(const float* a_src, const float* a_dst, int H, float negative_slope,
+                   const int32_t* rowptr, const int32_t* col, const int32_t* perm,
+                   int64_t n_rows, const float* row_max, const float* row_sum,
+                   float* alpha, pygb_stream_t s);
+
+/* GAT backward, per-edge part (dst-sorted rows, fp32): for slot p of row i
+ *   alpha_p recomputed;  dalpha_p = <g[i,h,:], xw[col[p],h,:]>
+ *   D[i,h] = <g[i,h,:], out[i,h,:] - bias[h,:]>   (= sum_p alpha_p dalpha_p)
+ *   ds_p = alpha_p (dalpha_p - D[i,h]) * leaky_relu'(a_dst[i,h] + a_src[col[p],h])
+ * alpha and ds are written as [E,H] in original edge order.  d_a_dst / d_a_src
+ * follow as segmented sums of ds (pygb_seg_gather_reduce with idx = perm) and
+ * d_xw as pygb_seg_gather_reduce_heads over the source-sorted CSR. */
+int pygb_gat_edge_grad(const float* xw, int64_t ldx, const float* a_src,
+                       const float* a_dst, int H, int C, float negative_slope,
+                       const int32_t* rowptr, const int32_t* col, const int32_t* perm,
+                       int64_t n_rows, const float* out, int64_t ldo, const float* bias,
+                       const float* grad_out, int64_t ldg, const float* row_max,
+                       const float* row_sum, float* alpha, float* ds, pygb_stream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYGB_H_ */

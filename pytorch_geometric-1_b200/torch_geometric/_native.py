@@ -1,0 +1,139 @@
+"""ctypes binding of the C ABI in ``include/pygb.h`` (``lib/libpygb.so``).
+
+This is the only place the Python host touches native code.  There is no CPU
+fallback: if the shared library is missing, or a tensor is not on a CUDA
+device, the call raises.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), 'lib', 'libpygb.so')
+
+F32, BF16 = 0, 1
+SUM, MEAN = 0, 1
+LOOPS_REMOVE, LOOPS_ADD, LOOPS_REMOVE_ADD, LOOPS_ADD_REMAINING = 0, 1, 2, 3
+
+_c = ctypes
+_P, _I, _L, _F, _Z = _c.c_void_p, _c.c_int, _c.c_int64, _c.c_float, _c.c_size_t
+
+# name -> (restype, argtypes) ; mirrors include/pygb.h one to one
+SIGNATURES = {
+    'pygb_abi_version': (_I, []),
+    'pygb_last_error': (_c.c_char_p, []),
+    'pygb_check_device': (_I, [_P, _P, _P]),
+    'pygb_count_self_loops': (_I, [_P, _L, _P, _P]),
+    'pygb_apply_loops_workspace': (_Z, [_L, _L]),
+    'pygb_apply_loops': (_I, [_P, _L, _L, _I, _L, _P, _F, _P, _P, _P, _Z, _P]),
+    'pygb_csr_build_workspace': (_Z, [_L, _L]),
+    'pygb_csr_build': (_I, [_P, _P, _L, _L, _L, _P, _P, _P, _P, _P, _Z, _P]),
+    'pygb_permute_f32': (_I, [_P, _P, _L, _P, _P]),
+    'pygb_degree': (_I, [_P, _L, _L, _I, _P, _P]),
+    'pygb_weighted_degree': (_I, [_P, _P, _P, _L, _P, _P]),
+    'pygb_gcn_norm': (_I, [_P, _P, _L, _L, _P, _P, _P]),
+    'pygb_seg_gather_reduce': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
+    'pygb_seg_gather_reduce_heads': (_I, [_I, _P, _L, _I, _I, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
+    'pygb_gather_rows': (_I, [_I, _P, _L, _L, _P, _L, _P, _L, _P]),
+    'pygb_seg_max': (_I, [_I, _P, _L, _L, _P, _P, _P, _L, _L, _F, _I, _P, _L, _P, _P]),
+    'pygb_seg_max_backward': (_I, [_P, _L, _P, _L, _L, _L, _P, _L, _P]),
+    'pygb_edge_softmax': (_I, [_P, _L, _P, _P, _L, _P, _P]),
+    'pygb_edge_softmax_backward': (_I, [_P, _P, _L, _P, _P, _L, _P, _P]),
+    'pygb_gat_scores': (_I, [_I, _P, _L, _P, _L, _I, _I, _P, _P, _P]),
+    'pygb_gat_forward': (_I, [_I, _P, _L, _P, _P, _I, _I, _F, _P, _P, _L, _P, _P, _L, _P, _P, _P]),
+    'pygb_gat_alpha': (_I, [_P, _P, _I, _F, _P, _P, _P, _L, _P, _P, _P, _P]),
+    'pygb_gat_edge_grad': (_I, [_P, _L, _P, _P, _I, _I, _F, _P, _P, _P, _L, _P, _L, _P, _P, _L,
+                                _P, _P, _P, _P, _P]),
+}
+
+_lib = None
+_lock = threading.Lock()
+_checked_devices = set()
+launches = 0  # number of native calls issued (bench.py reports it)
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libpygb.so (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise NativeError(
+                'libpygb.so not found at {} — build it with `python -c "import '
+                '__graft_entry__ as g; g.build()"` or `make -C '
+                'pytorch_geometric-1_b200/csrc`. There is no CPU fallback.'.format(LIB_PATH))
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        if lib.pygb_abi_version() != 1:
+            raise NativeError('libpygb.so ABI version mismatch')
+        _lib = lib
+    return _lib
+
+
+def _check_device(device):
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx in _checked_devices:
+        return
+    lib = load()
+    with torch.cuda.device(idx):
+        rc = lib.pygb_check_device(None, None, None)
+    if rc != 0:
+        raise NativeError(lib.pygb_last_error().decode())
+    _checked_devices.add(idx)
+
+
+def require_cuda(*tensors):
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise NativeError(
+                'torch_geometric (B200 build) runs on CUDA tensors only; got a {} '
+                'tensor. There is no CPU fallback.'.format(t.device))
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise NativeError('tensors on different devices: {} vs {}'.format(dev, t.device))
+    _check_device(dev)
+    return dev
+
+
+def ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def call(name, device, *args):
+    """Invoke ``name(*args, stream)`` on ``device``'s current stream."""
+    global launches
+    lib = load()
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream().cuda_stream
+        rc = getattr(lib, name)(*args, stream)
+    launches += 1
+    if rc != 0:
+        raise NativeError('{} failed ({}): {}'.format(name, rc, lib.pygb_last_error().decode()))
+
+
+def workspace(name, *args):
+    return int(getattr(load(), name)(*args))
+
+
+def dtype_code(t):
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise NativeError('unsupported feature dtype {} (float32 or bfloat16)'.format(t.dtype))

@@ -1,0 +1,173 @@
+"""Device-side graph structures for the B200 path.
+
+``CSR``  — a stable sort of E entries by an int64 key (``rowptr``, ``perm`` and
+optionally ``col``), produced by ``pygb_csr_build``.  Stability makes the order
+inside a row the ascending original edge id, i.e. the order in which the CPU
+reference (torch_scatter's sequential loop) visits them.
+
+``Adj``  — the two CSRs of one ``edge_index``: by aggregation index (forward)
+and, lazily, by the opposite row (transposed walk for the backward).
+
+Both are memoised on the identity of the index tensor (storage pointer, shape,
+version counter), so ``GATConv`` — which the reference rebuilds every forward —
+and the generic ``scatter_`` path sort once per graph.
+"""
+import collections
+import threading
+
+import torch
+
+from . import _native as nat
+
+
+class CSR(object):
+    __slots__ = ('rowptr', 'col', 'perm', 'n_rows', 'n_cols', 'E', '_keep')
+
+    def __init__(self, rowptr, col, perm, n_rows, n_cols, E, keep=None):
+        self.rowptr, self.col, self.perm = rowptr, col, perm
+        self.n_rows, self.n_cols, self.E = n_rows, n_cols, E
+        self._keep = keep
+
+    @property
+    def device(self):
+        return self.rowptr.device
+
+
+def build_csr(key, other, n_rows, n_cols=None):
+    """Sort ``key`` (int64 [E]) into a CSR with ``n_rows`` rows; ``other`` (int64
+    [E], optional) becomes ``col``.  Raises ``IndexError`` for out-of-range
+    indices (one device->host read of a status word per build)."""
+    dev = nat.require_cuda(key, other)
+    if key.dtype != torch.long or (other is not None and other.dtype != torch.long):
+        raise TypeError('index tensors must be int64')
+    E = key.numel()
+    n_rows = int(n_rows)
+    n_cols = int(n_cols) if n_cols is not None else n_rows
+    key = key if key.is_contiguous() else key.contiguous()
+    if other is not None and not other.is_contiguous():
+        other = other.contiguous()
+    rowptr = torch.empty(n_rows + 1, dtype=torch.int32, device=dev)
+    perm = torch.empty(E, dtype=torch.int32, device=dev)
+    col = torch.empty(E, dtype=torch.int32, device=dev) if other is not None else None
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    ws_bytes = nat.workspace('pygb_csr_build_workspace', E, n_rows)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    nat.call('pygb_csr_build', dev, nat.ptr(key), nat.ptr(other), E, n_rows, n_cols,
+             nat.ptr(rowptr), nat.ptr(perm), nat.ptr(col), nat.ptr(status), nat.ptr(ws), ws_bytes)
+    st = int(status.item())
+    if st == 1:
+        raise IndexError('index out of range: expected values in [0, {})'.format(n_rows))
+    if st == 2:
+        raise IndexError('index out of range: expected values in [0, {})'.format(n_cols))
+    return CSR(rowptr, col, perm, n_rows, n_cols, E)
+
+
+# --------------------------------------------------------------------------
+# memoisation keyed on tensor identity
+# --------------------------------------------------------------------------
+class _LRU(object):
+    def __init__(self, capacity):
+        self.capacity = capacity
+        self.data = collections.OrderedDict()
+        self.lock = threading.Lock()
+
+    def get(self, key):
+        with self.lock:
+            v = self.data.get(key)
+            if v is not None:
+                self.data.move_to_end(key)
+            return v
+
+    def put(self, key, value):
+        with self.lock:
+            self.data[key] = value
+            self.data.move_to_end(key)
+            while len(self.data) > self.capacity:
+                self.data.popitem(last=False)
+
+    def clear(self):
+        with self.lock:
+            self.data.clear()
+
+
+def _ident(t):
+    return (t.data_ptr(), tuple(t.shape), tuple(t.stride()), t._version, t.device.index)
+
+
+_csr_cache = _LRU(8)
+_adj_cache = _LRU(4)
+
+
+def clear_caches():
+    _csr_cache.clear()
+    _adj_cache.clear()
+
+
+def csr_for(index, n_rows):
+    """Memoised ``build_csr(index, None, n_rows)``."""
+    key = ('csr', _ident(index), int(n_rows))
+    hit = _csr_cache.get(key)
+    if hit is not None:
+        return hit
+    csr = build_csr(index, None, n_rows)
+    csr._keep = index  # pins the storage so the pointer cannot be recycled
+    _csr_cache.put(key, csr)
+    return csr
+
+
+class Adj(object):
+    """Adjacency of one ``edge_index`` for aggregation over row ``i``.
+
+    ``dst``: CSR keyed on ``edge_index[i]`` with ``col = edge_index[j]``.
+    ``src``: CSR keyed on ``edge_index[j]`` with ``col = edge_index[i]`` (lazy).
+    """
+
+    def __init__(self, edge_index, i, size):
+        self.edge_index = edge_index
+        self.i, self.j = i, 1 - i
+        self.size = (int(size[0]), int(size[1]))
+        self.E = edge_index.size(1)
+        self.dst = build_csr(edge_index[self.i], edge_index[self.j], self.size[self.i],
+                             self.size[self.j])
+        self._src = None
+        self._wcache = {}
+
+    @property
+    def n_dst(self):
+        return self.size[self.i]
+
+    @property
+    def n_src(self):
+        return self.size[self.j]
+
+    @property
+    def src(self):
+        if self._src is None:
+            ei = self.edge_index
+            self._src = build_csr(ei[self.j], ei[self.i], self.size[self.j], self.size[self.i])
+        return self._src
+
+    def permuted(self, w, which):
+        """``w[perm]`` for the 'dst' or 'src' order, memoised per weight tensor."""
+        key = (which, w.data_ptr(), w._version)
+        hit = self._wcache.get(key)
+        if hit is not None:
+            return hit[0]
+        csr = self.dst if which == 'dst' else self.src
+        out = torch.empty_like(w)
+        nat.call('pygb_permute_f32', w.device, nat.ptr(w), nat.ptr(csr.perm), w.numel(),
+                 nat.ptr(out))
+        if len(self._wcache) > 4:
+            self._wcache.clear()
+        self._wcache[key] = (out, w)
+        return out
+
+
+def adj_for(edge_index, i, size):
+    key = ('adj', _ident(edge_index), int(i), int(size[0]), int(size[1]))
+    hit = _adj_cache.get(key)
+    if hit is not None:
+        return hit
+    adj = Adj(edge_index, i, size)
+    _adj_cache.put(key, adj)
+    return adj

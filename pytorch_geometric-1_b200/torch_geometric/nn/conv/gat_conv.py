@@ -1,0 +1,137 @@
+import torch
+import torch.nn.functional as F
+from torch.nn import Parameter
+
+from ... import ops
+from ...graph import adj_for
+from ...utils import add_self_loops, remove_self_loops, softmax
+from ..inits import glorot, zeros
+from .message_passing import MessagePassing
+
+
+class GATConv(MessagePassing):
+    r"""Graph attention layer with the reference's signature (SURVEY A.10;
+    reference call sites ConvexPruning.py:209-214,221 and examples/ppi.py:22-28):
+    ``GATConv(in, out, heads=1, concat=True, negative_slope=0.2, dropout=0, bias=True)``
+    with parameters ``weight [in, heads*out]``, ``att [1, heads, 2*out]``, ``bias``.
+
+    The attention logits split into a target and a source half, so the whole
+    propagate (leaky-relu, per-target softmax, weighted sum) runs as one fused
+    kernel over the destination-sorted graph; no ``[E, ...]`` tensor is built.
+    With ``dropout > 0`` in training mode the attention coefficients must be
+    materialised for the random mask, and the layer takes the generic route.
+    """
+
+    def __init__(self, in_channels, out_channels, heads=1, concat=True, negative_slope=0.2,
+                 dropout=0, bias=True, **kwargs):
+        super(GATConv, self).__init__(aggr='add', **kwargs)
+
+        self.in_channels = in_channels
+        self.out_channels = out_channels
+        self.heads = heads
+        self.concat = concat
+        self.negative_slope = negative_slope
+        self.dropout = dropout
+
+        self.weight = Parameter(torch.Tensor(in_channels, heads * out_channels))
+        self.att = Parameter(torch.Tensor(1, heads, 2 * out_channels))
+
+        if bias and concat:
+            self.bias = Parameter(torch.Tensor(heads * out_channels))
+        elif bias and not concat:
+            self.bias = Parameter(torch.Tensor(out_channels))
+        else:
+            self.register_parameter('bias', None)
+
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        glorot(self.weight)
+        glorot(self.att)
+        zeros(self.bias)
+
+    def forward(self, x, edge_index, size=None):
+        """"""
+        if size is None and torch.is_tensor(x):
+            edge_index = self._with_self_loops(edge_index, x.size(self.node_dim))
+
+        if torch.is_tensor(x):
+            x = torch.matmul(x, self.weight)
+        else:
+            x = (None if x[0] is None else torch.matmul(x[0], self.weight),
+                 None if x[1] is None else torch.matmul(x[1], self.weight))
+
+        return self.propagate(edge_index, size=size, x=x)
+
+    def _with_self_loops(self, edge_index, num_nodes):
+        # remove_self_loops + add_self_loops, memoised on the edge_index identity
+        # (the reference redoes it every forward).
+        key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, num_nodes)
+        cache = self.__dict__.get('_loop_cache')
+        if cache is not None and cache[0] == key:
+            return cache[2]
+        ei, _ = remove_self_loops(edge_index)
+        ei, _ = add_self_loops(ei, num_nodes=num_nodes)
+        self.__dict__['_loop_cache'] = (key, edge_index, ei)
+        return ei
+
+    def _fused_propagate(self, edge_index, size, i, kwargs):
+        cls = type(self)
+        if (cls.message is not GATConv.message or cls.update is not GATConv.update
+                or self.node_dim != 0):
+            return NotImplemented
+        if self.training and self.dropout > 0:
+            return NotImplemented
+        x = kwargs.get('x')
+        j = 1 - i
+        if torch.is_tensor(x):
+            x_src = x_dst = x
+        else:
+            x_src, x_dst = x[j], x[i]
+        if x_src is None or x_src.dtype not in (torch.float32, torch.bfloat16):
+            return NotImplemented
+        adj = adj_for(edge_index, i, size)
+        fuse_bias = self.bias is not None and self.concat
+        out = ops.gat_propagate(x_src, x_dst, self.att, self.bias if fuse_bias else None, adj,
+                                self.heads, self.out_channels, self.negative_slope)
+        self._bias_fused = fuse_bias
+        return out.view(-1, self.heads, self.out_channels)
+
+    def message(self, edge_index_i, x_i, x_j, size_i):
+        # generic route (dropout on alpha, or user subclasses)
+        x_j = x_j.view(-1, self.heads, self.out_channels)
+        if x_i is None:
+            alpha = (x_j * self.att[:, :, self.out_channels:]).sum(dim=-1)
+        else:
+            x_i = x_i.view(-1, self.heads, self.out_channels)
+            alpha = (torch.cat([x_i, x_j], dim=-1) * self.att).sum(dim=-1)
+
+        alpha = F.leaky_relu(alpha, self.negative_slope)
+        alpha = softmax(alpha, edge_index_i, size_i)
+
+        alpha = F.dropout(alpha, p=self.dropout, training=self.training)
+
+        return x_j * alpha.view(-1, self.heads, 1)
+
+    def update(self, aggr_out):
+        if self.concat is True:
+            aggr_out = aggr_out.view(-1, self.heads * self.out_channels)
+        else:
+            aggr_out = aggr_out.mean(dim=1)
+
+        if getattr(self, '_bias_fused', False):
+            self._bias_fused = False
+            return aggr_out
+        if self.bias is not None:
+            aggr_out = aggr_out + self.bias
+        return aggr_out
+
+    def __getstate__(self):
+        state = self.__dict__.copy()
+        state.pop('_loop_cache', None)
+        state.pop('_bias_fused', None)
+        return state
+
+    def __repr__(self):
+        return '{}({}, {}, heads={})'.format(self.__class__.__name__, self.in_channels,
+                                             self.out_channels, self.heads)

@@ -1,0 +1,381 @@
+"""Tensor-level operators over the C ABI, with autograd.
+
+These are the pieces ``MessagePassing.propagate``, ``utils.scatter_`` and
+``utils.softmax`` are assembled from.  Everything here launches kernels of
+``libpygb.so`` on the tensor's current CUDA stream; there is no CPU path.
+"""
+import torch
+
+from . import _native as nat
+from .graph import adj_for, csr_for  # noqa: F401  (re-exported)
+
+NEG_INF = float('-inf')
+
+
+def _rows2d(x):
+    """View ``x`` as [n, F] with unit inner stride; returns (x2d, F)."""
+    n = x.size(0)
+    x2 = x.reshape(n, -1)
+    if x2.numel() > 0 and x2.stride(1) != 1:
+        x2 = x2.contiguous()
+    if x2.size(1) == 1 and x2.stride(0) < 1:
+        x2 = x2.contiguous()
+    return x2
+
+
+def _ld(x2):
+    return x2.stride(0) if x2.size(0) > 1 else max(x2.size(1), 1)
+
+
+def _f32(t):
+    if t is None:
+        return None
+    t = t if t.dtype == torch.float32 else t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+# --------------------------------------------------------------------------
+# raw (no autograd) launches
+# --------------------------------------------------------------------------
+def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=None,
+                          heads=None):
+    """out[i] = reduce_p w_p * x[idx[p]] over the rows of ``csr``."""
+    dev = nat.require_cuda(x, idx, w, bias)
+    x2 = _rows2d(x)
+    F = x2.size(1)
+    out = torch.empty((csr.n_rows, F), dtype=x2.dtype, device=dev)
+    if csr.n_rows == 0 or F == 0:
+        return out
+    if csr.E == 0:
+        out.zero_()
+        if bias is not None:
+            out += bias.to(out.dtype)
+        return out
+    dt = nat.dtype_code(x2)
+    w = _f32(w)
+    bias = _f32(bias)
+    if heads is None:
+        nat.call('pygb_seg_gather_reduce', dev, nat.MEAN if reduce == 'mean' else nat.SUM, dt,
+                 nat.ptr(x2), _ld(x2), F, nat.ptr(csr.rowptr), nat.ptr(idx), nat.ptr(w),
+                 nat.ptr(wperm), nat.ptr(bias), csr.n_rows, nat.ptr(out), F)
+    else:
+        H, C = heads
+        assert H * C == F and reduce == 'sum'
+        nat.call('pygb_seg_gather_reduce_heads', dev, dt, nat.ptr(x2), _ld(x2), H, C,
+                 nat.ptr(csr.rowptr), nat.ptr(idx), nat.ptr(w), nat.ptr(wperm), nat.ptr(bias),
+                 csr.n_rows, nat.ptr(out), F)
+    return out
+
+
+def gather_rows_raw(x, index):
+    dev = nat.require_cuda(x, index)
+    x2 = _rows2d(x)
+    F = x2.size(1)
+    E = index.numel()
+    out = torch.empty((E, F), dtype=x2.dtype, device=dev)
+    if E > 0 and F > 0:
+        index = index if index.is_contiguous() else index.contiguous()
+        nat.call('pygb_gather_rows', dev, nat.dtype_code(x2), nat.ptr(x2), _ld(x2), F,
+                 nat.ptr(index), E, nat.ptr(out), F)
+    return out
+
+
+def seg_max_raw(src, csr, idx, eid, e_fill, zero_below=NEG_INF, mask_arg=False, want_arg=True):
+    dev = nat.require_cuda(src, idx, eid)
+    s2 = _rows2d(src)
+    F = s2.size(1)
+    out = torch.empty((csr.n_rows, F), dtype=s2.dtype, device=dev)
+    arg = torch.empty((csr.n_rows, F), dtype=torch.long, device=dev) if want_arg else None
+    if csr.n_rows > 0 and F > 0:
+        nat.call('pygb_seg_max', dev, nat.dtype_code(s2), nat.ptr(s2), _ld(s2), F,
+                 nat.ptr(csr.rowptr), nat.ptr(idx), nat.ptr(eid), csr.n_rows, int(e_fill),
+                 float(zero_below), int(bool(mask_arg)), nat.ptr(out), F, nat.ptr(arg))
+    return out, arg
+
+
+def _row_counts(csr, dtype):
+    cnt = (csr.rowptr[1:] - csr.rowptr[:-1]).clamp(min=1)
+    return cnt.to(dtype).unsqueeze(1)
+
+
+# --------------------------------------------------------------------------
+# fused propagate for messages of the form  w_e * x_j   (GCNConv and the default)
+# --------------------------------------------------------------------------
+class _GatherReduce(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias, adj, reduce):
+        shape = x.shape
+        w_csr = adj.permuted(_f32(w), 'dst') if w is not None else None
+        out = seg_gather_reduce_raw(x, adj.dst, adj.dst.col, reduce, w_csr, None, bias)
+        ctx.adj, ctx.reduce = adj, reduce
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x if (w is not None and w.requires_grad) else None, w)
+        ctx.xshape = shape
+        return out.view((adj.n_dst,) + tuple(shape[1:]))
+
+    @staticmethod
+    def backward(ctx, g):
+        adj, reduce = ctx.adj, ctx.reduce
+        x, w = ctx.saved_tensors
+        g2 = _rows2d(g)
+        gx = gw = gb = None
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = g2.sum(0)
+        gs = g2 / _row_counts(adj.dst, g2.dtype) if reduce == 'mean' else g2
+        if ctx.needs_input_grad[0]:
+            w_t = adj.permuted(_f32(w), 'src') if w is not None else None
+            gx = seg_gather_reduce_raw(gs, adj.src, adj.src.col, 'sum', w_t, None, None)
+            gx = gx.view((adj.n_src,) + tuple(ctx.xshape[1:]))
+        if w is not None and ctx.needs_input_grad[1]:
+            ei = adj.edge_index
+            gi = gather_rows_raw(gs, ei[adj.i])
+            xj = gather_rows_raw(x, ei[adj.j])
+            gw = (gi.float() * xj.float()).sum(1).to(w.dtype)
+        return gx, gw, gb, None, None
+
+
+def gather_reduce(x, adj, w=None, reduce='sum', bias=None):
+    """``scatter_(reduce, w.view(-1,1) * x[edge_index[j]], edge_index[i])`` fused
+    (SURVEY A.1 step 2+6, A.9 message/update)."""
+    return _GatherReduce.apply(x, w, bias, adj, reduce)
+
+
+# --------------------------------------------------------------------------
+# gathers for generic message() functions
+# --------------------------------------------------------------------------
+class _GatherRows(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, index):
+        ctx.n = x.size(0)
+        ctx.xshape = x.shape
+        ctx.save_for_backward(index)
+        out = gather_rows_raw(x, index)
+        return out.view((index.numel(),) + tuple(x.shape[1:]))
+
+    @staticmethod
+    def backward(ctx, g):
+        (index,) = ctx.saved_tensors
+        csr = csr_for(index, ctx.n)
+        gx = seg_gather_reduce_raw(g, csr, csr.perm, 'sum')
+        return gx.view(ctx.xshape), None
+
+
+def index_select0(x, index):
+    """``torch.index_select(x, 0, index)`` (A.1 step 2) with an atomic-free backward."""
+    return _GatherRows.apply(x, index)
+
+
+# --------------------------------------------------------------------------
+# scatter of a materialised message tensor (generic path, A.3-A.6)
+# --------------------------------------------------------------------------
+class _SegReduce(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, src, index, dim_size, name, zero_below):
+        csr = csr_for(index, dim_size)
+        E = index.numel()
+        ctx.csr, ctx.name, ctx.E = csr, name, E
+        ctx.sshape = src.shape
+        tail = tuple(src.shape[1:])
+        if name in ('add', 'mean'):
+            out = seg_gather_reduce_raw(src, csr, csr.perm, 'mean' if name == 'mean' else 'sum')
+            ctx.save_for_backward(index)
+        else:
+            s = src if name == 'max' else -src
+            out, arg = seg_max_raw(s, csr, csr.perm, csr.perm, E, zero_below, True)
+            if name == 'min':
+                out = -out
+            ctx.save_for_backward(arg)
+        return out.view((dim_size,) + tail)
+
+    @staticmethod
+    def backward(ctx, g):
+        name, csr = ctx.name, ctx.csr
+        g2 = _rows2d(g)
+        if name in ('add', 'mean'):
+            (index,) = ctx.saved_tensors
+            if name == 'mean':
+                g2 = g2 / _row_counts(csr, g2.dtype)
+            gs = gather_rows_raw(g2, index)
+        else:
+            (arg,) = ctx.saved_tensors
+            gf = _f32(g2)
+            if name == 'min':
+                pass  # d(-max(-x))/dx routes +g to the arg position
+            F = gf.size(1)
+            gs = torch.zeros((ctx.E, F), dtype=torch.float32, device=g.device)
+            if ctx.E > 0 and F > 0:
+                nat.call('pygb_seg_max_backward', g.device, nat.ptr(gf), _ld(gf), nat.ptr(arg),
+                         csr.n_rows, F, ctx.E, nat.ptr(gs), F)
+            gs = gs.to(g.dtype)
+        return gs.view(ctx.sshape), None, None, None, None
+
+
+def segment_reduce(src, index, dim_size, name, zero_below=NEG_INF):
+    return _SegReduce.apply(src, index, int(dim_size), name, zero_below)
+
+
+def scatter_max(src, index, dim_size):
+    """torch_scatter.scatter_max semantics (A.6): (values, argmax), first maximum
+    wins, empty rows -> 0 / E.  Not differentiable through this entry point."""
+    csr = csr_for(index, dim_size)
+    out, arg = seg_max_raw(src, csr, csr.perm, csr.perm, index.numel())
+    tail = tuple(src.shape[1:])
+    return out.view((dim_size,) + tail), arg.view((dim_size,) + tail)
+
+
+# --------------------------------------------------------------------------
+# fused gather-max for the default message (x_j) with aggr='max'
+# --------------------------------------------------------------------------
+class _GatherMax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, adj, zero_below):
+        csr = adj.dst
+        out, arg = seg_max_raw(x, csr, csr.col, csr.perm, adj.E, zero_below, True)
+        ctx.adj, ctx.xshape = adj, x.shape
+        ctx.save_for_backward(arg)
+        return out.view((adj.n_dst,) + tuple(x.shape[1:]))
+
+    @staticmethod
+    def backward(ctx, g):
+        (arg,) = ctx.saved_tensors
+        adj = ctx.adj
+        gf = _f32(_rows2d(g))
+        F = gf.size(1)
+        ge = torch.zeros((adj.E, F), dtype=torch.float32, device=g.device)
+        if adj.E > 0 and F > 0:
+            nat.call('pygb_seg_max_backward', g.device, nat.ptr(gf), _ld(gf), nat.ptr(arg),
+                     adj.n_dst, F, adj.E, nat.ptr(ge), F)
+        csr = csr_for(adj.edge_index[adj.j], adj.n_src)
+        gx = seg_gather_reduce_raw(ge, csr, csr.perm, 'sum').to(g.dtype)
+        return gx.view(ctx.xshape), None, None
+
+
+def gather_max(x, adj, zero_below=-10000.0):
+    return _GatherMax.apply(x, adj, zero_below)
+
+
+# --------------------------------------------------------------------------
+# utils.softmax (A.7)
+# --------------------------------------------------------------------------
+class _EdgeSoftmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, src, index, num_nodes):
+        dev = nat.require_cuda(src, index)
+        csr = csr_for(index, num_nodes)
+        s2 = _f32(_rows2d(src))
+        H = s2.size(1)
+        out = torch.empty_like(s2)
+        if s2.numel() > 0:
+            nat.call('pygb_edge_softmax', dev, nat.ptr(s2), H, nat.ptr(csr.rowptr),
+                     nat.ptr(csr.perm), csr.n_rows, nat.ptr(out))
+        ctx.csr = csr
+        ctx.save_for_backward(out)
+        ctx.sdtype = src.dtype
+        return out.to(src.dtype).view(src.shape)
+
+    @staticmethod
+    def backward(ctx, g):
+        (y,) = ctx.saved_tensors
+        csr = ctx.csr
+        g2 = _f32(_rows2d(g))
+        gs = torch.empty_like(y)
+        if y.numel() > 0:
+            nat.call('pygb_edge_softmax_backward', g.device, nat.ptr(y), nat.ptr(g2), y.size(1),
+                     nat.ptr(csr.rowptr), nat.ptr(csr.perm), csr.n_rows, nat.ptr(gs))
+        return gs.to(ctx.sdtype).view(g.shape), None, None
+
+
+def edge_softmax(src, index, num_nodes):
+    return _EdgeSoftmax.apply(src, index, int(num_nodes))
+
+
+# --------------------------------------------------------------------------
+# fused GAT propagate (A.10)
+# --------------------------------------------------------------------------
+def _gat_scores(xw2, att2, H, C, want_dst=True):
+    dev = xw2.device
+    n = xw2.size(0)
+    a_src = torch.empty((n, H), dtype=torch.float32, device=dev)
+    a_dst = torch.empty((n, H), dtype=torch.float32, device=dev) if want_dst else None
+    if n > 0:
+        nat.call('pygb_gat_scores', dev, nat.dtype_code(xw2), nat.ptr(xw2), _ld(xw2),
+                 nat.ptr(att2), n, H, C, nat.ptr(a_src), nat.ptr(a_dst))
+    return a_src, a_dst
+
+
+class _GATFused(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_src, x_dst, att, bias, adj, H, C, slope, same):
+        dev = nat.require_cuda(x_src, x_dst, att, bias)
+        xs = _rows2d(x_src)
+        att2 = _f32(att.reshape(H, 2 * C))
+        a_src, a_dst = _gat_scores(xs, att2, H, C, want_dst=same)
+        if not same and x_dst is not None:
+            _, a_dst = _gat_scores(_rows2d(x_dst), att2, H, C, want_dst=True)
+        n_dst = adj.n_dst
+        F = H * C
+        out = torch.empty((n_dst, F), dtype=xs.dtype, device=dev)
+        row_max = torch.empty((n_dst, H), dtype=torch.float32, device=dev)
+        row_sum = torch.empty((n_dst, H), dtype=torch.float32, device=dev)
+        bias2 = _f32(bias)
+        if n_dst > 0:
+            nat.call('pygb_gat_forward', dev, nat.dtype_code(xs), nat.ptr(xs), _ld(xs),
+                     nat.ptr(a_src), nat.ptr(a_dst), H, C, float(slope), nat.ptr(adj.dst.rowptr),
+                     nat.ptr(adj.dst.col), n_dst, nat.ptr(bias2), nat.ptr(out), F,
+                     nat.ptr(row_max), nat.ptr(row_sum))
+        ctx.adj, ctx.H, ctx.C, ctx.slope, ctx.same = adj, H, C, slope, same
+        ctx.att_shape = att.shape
+        ctx.save_for_backward(x_src, None if same else x_dst, att2, bias2, a_src, a_dst, out,
+                              row_max, row_sum)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x_src, x_dst, att2, bias2, a_src, a_dst, out, row_max, row_sum = ctx.saved_tensors
+        adj, H, C, slope = ctx.adj, ctx.H, ctx.C, ctx.slope
+        dev = g.device
+        F = H * C
+        gf = _f32(_rows2d(g))
+        xs = _f32(_rows2d(x_src))
+        outf = _f32(out)
+        E = adj.E
+        alpha = torch.empty((E, H), dtype=torch.float32, device=dev)
+        ds = torch.empty((E, H), dtype=torch.float32, device=dev)
+        dst = adj.dst
+        if adj.n_dst > 0 and E > 0:
+            nat.call('pygb_gat_edge_grad', dev, nat.ptr(xs), _ld(xs), nat.ptr(a_src),
+                     nat.ptr(a_dst), H, C, float(slope), nat.ptr(dst.rowptr), nat.ptr(dst.col),
+                     nat.ptr(dst.perm), adj.n_dst, nat.ptr(outf), F, nat.ptr(bias2), nat.ptr(gf),
+                     _ld(gf), nat.ptr(row_max), nat.ptr(row_sum), nat.ptr(alpha), nat.ptr(ds))
+        src = adj.src
+        # d_xw[j] = sum_p alpha_p * g[dst_p]   (transposed walk, per-head weights)
+        d_xs = seg_gather_reduce_raw(gf, src, src.col, 'sum', alpha, src.perm, None, (H, C))
+        d_a_src = seg_gather_reduce_raw(ds, src, src.perm, 'sum')          # [n_src, H]
+        att_d, att_s = att2[:, :C], att2[:, C:]
+        d_xs = d_xs.view(-1, H, C) + d_a_src.unsqueeze(-1) * att_s.unsqueeze(0)
+        d_att_s = torch.einsum('nh,nhc->hc', d_a_src, xs.view(-1, H, C))
+        d_xd = None
+        d_att_d = torch.zeros_like(d_att_s)
+        if a_dst is not None:
+            d_a_dst = seg_gather_reduce_raw(ds, dst, dst.perm, 'sum')      # [n_dst, H]
+            xd = xs if ctx.same else _f32(_rows2d(x_dst))
+            d_att_d = torch.einsum('nh,nhc->hc', d_a_dst, xd.view(-1, H, C))
+            dd = d_a_dst.unsqueeze(-1) * att_d.unsqueeze(0)
+            if ctx.same:
+                d_xs = d_xs + dd
+            else:
+                d_xd = dd.reshape(-1, F).to(x_dst.dtype)
+        d_att = torch.cat([d_att_d, d_att_s], dim=1).view(ctx.att_shape)
+        d_bias = gf.sum(0) if bias2 is not None else None
+        d_xs = d_xs.reshape(-1, F).to(x_src.dtype)
+        if ctx.same:
+            # x was passed twice (as x_src and x_dst): give all of it to x_src
+            return d_xs, None, d_att, d_bias, None, None, None, None, None
+        return d_xs, d_xd, d_att, d_bias, None, None, None, None, None
+
+
+def gat_propagate(x_src, x_dst, att, bias, adj, H, C, slope):
+    """Fused GATConv message+softmax+aggregate (A.10).  ``x_dst`` is ``x_src``
+    itself (ordinary graphs), another tensor (bipartite) or None (x_i = None)."""
+    same = x_dst is x_src
+    return _GATFused.apply(x_src, None if same else x_dst, att, bias, adj, H, C, slope, same)
