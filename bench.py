@@ -1,0 +1,399 @@
+#!/usr/bin/env python
+"""bench.py — propagate edges/sec on the BASELINE.json workload.
+
+Workload (BASELINE.json configs[4], the one the metric "propagate edges/sec at
+1/2/4/8 B200" is quoted on; it fits one GPU): 3-layer GCNConv, hidden 256, on the
+synthetic ogbn-products-shaped power-law graph (2,449,029 nodes, 62M directed
+edges, 100 input features, 47 classes).  One *step* = one forward pass of the
+3-layer model = three `MessagePassing.propagate` calls (aggregation widths 256,
+256, 47) plus the X·W transforms; `value` = 3·E' edges aggregated per step / time.
+At N>1 GPUs the graph is 1-D partitioned by destination range (strong scaling,
+fixed graph) with an all-gather of the source features per layer.
+
+  python bench.py --gpus N --steps K --warmup W            # this framework (CUDA)
+  python bench.py --impl reference --gpus N --steps K ...  # the CPU reference arm
+
+The reference arm times the oracle (a torch-CPU port of the pinned
+torch-geometric 1.4.3 / torch-scatter 2.0.4 path — the reference's own code for
+the path is not vendored and not installable here) on the host cores, on a
+1/16-scale graph of the same family (bounded sample).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'pytorch_geometric-1_b200'))
+
+import torch  # noqa: E402
+import torch.nn.functional as F  # noqa: E402
+
+WORKLOADS = {
+    # name: (nodes, undirected pairs, in features, hidden, classes)
+    'products': (2449029, 31000000, 100, 256, 47),
+    'products_small': (2449029 // 16, 31000000 // 16, 100, 256, 47),
+    'tiny': (20000, 200000, 100, 256, 47),
+}
+METRIC = 'propagate_edges_per_sec'
+UNIT = 'edges/s'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--workload', default='products', choices=sorted(WORKLOADS))
+    ap.add_argument('--dtype', default='f32', choices=['f32', 'bf16'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ----------------------------------------------------------------------------
+class ClockSampler(object):
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+    NAMES = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                 '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(',')]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, v in zip(self.NAMES, parts[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        return {'sm_mhz': statistics.median(sm) if sm else None,
+                'sm_max_mhz': max(mx) if mx else None, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+# ----------------------------------------------------------------------------
+# reference arm / cpu baseline: the oracle on host cores
+# ----------------------------------------------------------------------------
+def cpu_reference(steps, warmup, sample='products_small'):
+    from oracle import ref_cpu as O
+    from torch_geometric.datasets import synthetic
+    n, pairs, fin, hid, ncls = WORKLOADS[sample]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    data = synthetic.products_like(seed=4, device='cpu', num_nodes=n, num_pairs=pairs,
+                                   num_features=fin)
+    torch.manual_seed(0)
+    convs = [O.GCNConv(fin, hid, cached=True), O.GCNConv(hid, hid, cached=True),
+             O.GCNConv(hid, ncls, cached=True)]
+
+    def forward():
+        with torch.no_grad():
+            h = data.x
+            for k, c in enumerate(convs):
+                h = c(h, data.edge_index)
+                if k < 2:
+                    h = F.relu(h)
+            return F.log_softmax(h, dim=1)
+
+    forward()  # builds the cached normalisation (untimed, like the GPU arm)
+    e_prime = convs[0].cached_result[0].size(1)
+    for _ in range(max(warmup - 1, 0)):
+        forward()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        forward()
+    dt = time.perf_counter() - t0
+    value = 3.0 * e_prime * steps / dt
+    desc = ('oracle (torch-CPU port of PyG 1.4.3 propagate + torch_scatter 2.0.4) 3-layer GCN '
+            'forward on a 1/16-scale products-shaped graph: {} nodes, {} edges after self-loops'
+            .format(n, e_prime))
+    return value, dt / steps * 1e3, cores, desc, e_prime
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 3))
+    warmup = max(1, min(args.warmup, 1))
+    value, ms, cores, desc, _ = cpu_reference(steps, warmup)
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': steps, 'warmup': warmup, 'ms_per_step': ms, 'higher_is_better': True,
+        'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': '3-layer GCNConv hidden 256, products-shaped power-law graph '
+                               '(BASELINE configs[4]); bounded sample: ' + desc},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                         'sample': desc},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------
+# the B200 arm
+# ----------------------------------------------------------------------------
+def peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+        except Exception:
+            pass
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def k1_bytes(e_edges, n_rows, F, itemsize, weighted=True):
+    """SURVEY §8d algorithmic bytes of one K1 launch."""
+    return e_edges * (4 + (4 if weighted else 0)) + e_edges * F * itemsize + \
+        n_rows * F * itemsize + (n_rows + 1) * 4
+
+
+def run_b200(args):
+    import torch.distributed as dist
+    import torch_geometric  # noqa: F401
+    from torch_geometric import _native as nat
+    from torch_geometric.datasets import synthetic
+    from torch_geometric.nn import GCNConv
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py (impl b200) needs a CUDA device; there is no CPU path. '
+                         'Use --impl reference for the CPU arm.')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    nat.load()
+
+    n, pairs, fin, hid, ncls = WORKLOADS[args.workload]
+    dtype = torch.float32 if args.dtype == 'f32' else torch.bfloat16
+    itemsize = 4 if args.dtype == 'f32' else 2
+
+    # ---- setup (untimed): graph, model, cached normalisation + sorted graph ----
+    data = synthetic.products_like(seed=4, device=dev, num_nodes=n, num_pairs=pairs,
+                                   num_features=fin)
+    torch.manual_seed(0)
+    convs = [GCNConv(fin, hid, cached=True), GCNConv(hid, hid, cached=True),
+             GCNConv(hid, ncls, cached=True)]
+    convs = [c.to(dev).to(dtype) for c in convs]
+    x_dev = data.x.to(dtype)
+    edge_index = data.edge_index
+    del data
+
+    if world == 1:
+        def forward(x):
+            with torch.no_grad():
+                h = x
+                for k, c in enumerate(convs):
+                    h = c(h, edge_index)
+                    if k < 2:
+                        h = F.relu(h)
+                return F.log_softmax(h.float(), dim=1)
+
+        forward(x_dev)
+        e_prime = convs[0].cached_result[0].size(1)
+        # the three layers share one sorted graph: same cached edge_index' object
+        ei_shared, norm_shared = convs[0].cached_result
+        for c in convs[1:]:
+            c.cached_result = (ei_shared, norm_shared)
+        edge_index = edge_index  # keep: cached=True checks its edge count every call
+        n_rows_local = n
+        x_in = x_dev
+    else:
+        from torch_geometric.dist import DistGraph, dist_gcn_layer
+        ei_full, norm_full = GCNConv.norm(edge_index, n, None, False, torch.float32)
+        e_prime = ei_full.size(1)
+        graph = DistGraph(ei_full, norm_full, n, rank, world)
+        x_in = graph.local_rows(x_dev).contiguous()
+        n_rows_local = graph.plan.n_local
+        del ei_full, norm_full, edge_index, x_dev
+        torch.cuda.empty_cache()
+
+        def forward(x):
+            with torch.no_grad():
+                h = x
+                for k, c in enumerate(convs):
+                    h = dist_gcn_layer(graph, h, c.weight, c.bias)
+                    if k < 2:
+                        h = F.relu(h)
+                return F.log_softmax(h.float(), dim=1)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        out = forward(x_in)
+    barrier()
+
+    # ---- timed region: EXACTLY K steps, CUDA events, max over ranks -----------
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    nat.event_log = []
+    l0 = nat.launches
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.nvtx.range_push('timed')
+    ev0.record()
+    for _ in range(args.steps):
+        out = forward(x_in)
+    ev1.record()
+    barrier()
+    torch.cuda.nvtx.range_pop()
+    elapsed_ms = ev0.elapsed_time(ev1)
+    launches = nat.launches - l0
+    log, nat.event_log = nat.event_log, None
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([elapsed_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+    ms_per_step = elapsed_ms / args.steps
+    value = 3.0 * e_prime / (ms_per_step * 1e-3)
+
+    # ---- roofline of the dominant kernel: K1 at F = hidden ---------------------
+    k1 = [(e0.elapsed_time(e1), a) for (name, a, e0, e1) in log
+          if name == 'pygb_seg_gather_reduce' and a[4] == hid]
+    k1_ms = sum(t for t, _ in k1) / max(len(k1), 1)
+    all_k1_ms = sum(e0.elapsed_time(e1) for (name, a, e0, e1) in log
+                    if name == 'pygb_seg_gather_reduce') / args.steps
+    e_local = e_prime if world == 1 else graph.num_edges_local
+    bytes_k1 = k1_bytes(e_local, n_rows_local, hid, itemsize)
+    peak, peak_src = peaks()
+    achieved = bytes_k1 / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, 'profiles', 'k1_traffic.json')
+    if os.path.exists(tpath) and world == 1 and args.workload == 'products':
+        try:
+            traffic = json.load(open(tpath)).get(args.dtype)
+        except Exception:
+            traffic = None
+    roofline = {'bound': 'hbm', 'kernel': 'seg_gather_reduce_kernel (K1), F=%d %s' % (hid, args.dtype),
+                'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                'frac_of_nominal_8000': achieved / 8000.0, 'peak_source': peak_src,
+                'algorithmic_bytes_per_launch': bytes_k1, 'avg_launch_ms': k1_ms,
+                'k1_share_of_step': all_k1_ms / ms_per_step if ms_per_step > 0 else None,
+                'traffic': traffic}
+
+    # ---- end to end: host buffers -> public API -> host result ----------------
+    e2e = None
+    if not args.no_e2e:
+        x_host = x_in.cpu().pin_memory()
+        out_host = torch.empty(out.shape, dtype=out.dtype).pin_memory()
+        x_stage = torch.empty_like(x_in)
+
+        def e2e_step():
+            x_stage.copy_(x_host, non_blocking=True)
+            o = forward(x_stage)
+            out_host.copy_(o, non_blocking=True)
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        k = max(3, min(args.steps, 10))
+        ev0.record()
+        for _ in range(k):
+            e2e_step()
+        ev1.record()
+        barrier()
+        e_ms = ev0.elapsed_time(ev1)
+        if world > 1:
+            t = torch.tensor([e_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e_ms = float(t.item())
+        e2e = {'value': 3.0 * e_prime / (e_ms / k * 1e-3), 'unit': UNIT,
+               'h2d_bytes_per_step': x_host.numel() * x_host.element_size() * world,
+               'd2h_bytes_per_step': out_host.numel() * out_host.element_size() * world,
+               'ms_per_step': e_ms / k, 'steps': k}
+
+    # ---- cpu baseline (rank 0, N=1 only): bounded sample on the host cores -----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, ms, cores, desc, _ = cpu_reference(2, 1)
+        cpu = {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': desc,
+               'ms_per_step': ms}
+
+    if rank == 0:
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': max(args.warmup, 3), 'ms_per_step': ms_per_step, 'higher_is_better': True,
+            'scaling': 'strong', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
+            'config': {
+                'workload': '3-layer GCNConv (100->256->256->47, cached=True, relu) forward on the '
+                            'synthetic products-shaped power-law graph: %d nodes, %d directed '
+                            'edges, %d after self-loops (BASELINE configs[4])' %
+                            (n, 2 * pairs, e_prime),
+                'name': args.workload,
+                'edges_per_step': 3 * e_prime,
+                'parallelism': 'single GPU' if world == 1 else
+                               'dst-range partition x%d + all-gather halo (NCCL)' % world,
+                'l2': 'inputs larger than L2 (X\' = %.2f GB per layer vs 126 MB L2); no flush' %
+                      (n * hid * itemsize / 1e9),
+            },
+            'roofline': roofline, 'cpu_baseline': cpu, 'e2e': e2e, 'gpu_launches': launches,
+            'clocks': clocks,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -88,8 +88,16 @@ def add_remaining_self_loops(edge_index, edge_weight=None, fill_value=1,
                             device=edge_index.device)
         remaining = edge_weight[inv_mask]
         if remaining.numel() > 0:
-            # CPU index_put_ walks the indices in order -> last write wins (Q1)
-            loop_w[row[inv_mask]] = remaining
+            # Reference: `loop_weight[row[inv_mask]] = remaining`.  With several
+            # loops on one node the winner is order dependent (Q1): sequential
+            # index_put_ keeps the last one, a multi-threaded one may not.  The
+            # oracle pins the sequential answer: the loop with the highest edge id.
+            E = edge_index.size(1)
+            eid = torch.arange(E, device=row.device)[inv_mask]
+            last = torch.full((n,), -1, dtype=torch.long, device=row.device)
+            last = last.scatter_reduce(0, row[inv_mask], eid, 'amax', include_self=True)
+            has = last >= 0
+            loop_w = torch.where(has, edge_weight[last.clamp(min=0)], loop_w)
         edge_weight = torch.cat([edge_weight[mask], loop_w], dim=0)
     loop = torch.arange(0, n, dtype=row.dtype, device=row.device)
     loop = loop.unsqueeze(0).repeat(2, 1)

@@ -425,6 +425,8 @@ int pygb_apply_loops(const int64_t* edge_index, int64_t E, int64_t N, int mode, 
   PYGB_REQUIRE(E >= 0 && N >= 0 && mode >= 0 && mode <= 3, "pygb_apply_loops: bad arguments");
   PYGB_REQUIRE(edge_weight == nullptr || out_edge_weight != nullptr,
                "pygb_apply_loops: out_edge_weight missing");
+  PYGB_REQUIRE(out_edge_weight == nullptr || edge_weight != nullptr || E == 0,
+               "pygb_apply_loops: edge_weight missing");
   PYGB_REQUIRE(E < (1ll << 31) && N < (1ll << 31), "pygb_apply_loops: E, N must be < 2^31");
   cudaStream_t st = as_stream(s);
   if (ws_bytes < pygb_apply_loops_workspace(E, N)) {
@@ -442,7 +444,7 @@ int pygb_apply_loops(const int64_t* edge_index, int64_t E, int64_t N, int mode, 
   const int64_t* row = edge_index;
   const int64_t* col = edge_index + E;
   const float* w_in = edge_weight;
-  float* w_out = edge_weight ? out_edge_weight : nullptr;
+  float* w_out = out_edge_weight;
 
   if (remove) {
     if (E > 0) {

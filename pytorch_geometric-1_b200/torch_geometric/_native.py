@@ -52,6 +52,9 @@ _lib = None
 _lock = threading.Lock()
 _checked_devices = set()
 launches = 0  # number of native calls issued (bench.py reports it)
+# Optional profiler: a list that receives (name, info, start_event, end_event) for
+# every native call — CUDA events recorded on the launching stream (bench.py).
+event_log = None
 
 
 class NativeError(RuntimeError):
@@ -120,8 +123,16 @@ def call(name, device, *args):
     global launches
     lib = load()
     with torch.cuda.device(device):
-        stream = torch.cuda.current_stream().cuda_stream
-        rc = getattr(lib, name)(*args, stream)
+        cur = torch.cuda.current_stream()
+        if event_log is not None:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(cur)
+            rc = getattr(lib, name)(*args, cur.cuda_stream)
+            e1.record(cur)
+            event_log.append((name, args, e0, e1))
+        else:
+            rc = getattr(lib, name)(*args, cur.cuda_stream)
     launches += 1
     if rc != 0:
         raise NativeError('{} failed ({}): {}'.format(name, rc, lib.pygb_last_error().decode()))

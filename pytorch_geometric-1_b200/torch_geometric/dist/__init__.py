@@ -1,0 +1,5 @@
+from .partition import PartitionPlan, balanced_bounds
+from .halo import HaloExchange
+from .gcn import DistGraph, dist_gcn_layer
+
+__all__ = ['PartitionPlan', 'balanced_bounds', 'HaloExchange', 'DistGraph', 'dist_gcn_layer']

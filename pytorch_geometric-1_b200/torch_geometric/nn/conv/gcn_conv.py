@@ -77,7 +77,15 @@ class GCNConv(MessagePassing):
 
     def forward(self, x, edge_index, edge_weight=None):
         """"""
-        x = torch.matmul(x, self.weight)
+        # X·W with the output row padded to 16 bytes so that the aggregation stays on
+        # its 128-bit load path for widths like 7 or 47 (the padding is sliced away).
+        vec = 16 // x.element_size() if x.is_floating_point() else 1
+        pad = (-self.out_channels) % vec if self.out_channels > 1 else 0
+        if pad and x.dim() == 2:
+            w = torch.nn.functional.pad(self.weight, (0, pad))
+            x = torch.matmul(x, w)[:, :self.out_channels]
+        else:
+            x = torch.matmul(x, self.weight)
 
         if self.cached and self.cached_result is not None:
             if edge_index.size(1) != self.cached_num_edges:

@@ -15,12 +15,27 @@ NEG_INF = float('-inf')
 def _rows2d(x):
     """View ``x`` as [n, F] with unit inner stride; returns (x2d, F)."""
     n = x.size(0)
+    if x.numel() == 0:
+        f = 1
+        for d in x.shape[1:]:
+            f *= d
+        return x.new_empty((n, f))
     x2 = x.reshape(n, -1)
     if x2.numel() > 0 and x2.stride(1) != 1:
         x2 = x2.contiguous()
     if x2.size(1) == 1 and x2.stride(0) < 1:
         x2 = x2.contiguous()
     return x2
+
+
+def _unflat(out2, n, tail):
+    """[n, F] (possibly a padded-row view) -> [n, *tail]."""
+    tail = tuple(tail)
+    if len(tail) == 1:
+        return out2
+    if len(tail) == 0:
+        return out2.reshape(n)
+    return out2.reshape((n,) + tail)
 
 
 def _ld(x2):
@@ -43,7 +58,11 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
     dev = nat.require_cuda(x, idx, w, bias)
     x2 = _rows2d(x)
     F = x2.size(1)
-    out = torch.empty((csr.n_rows, F), dtype=x2.dtype, device=dev)
+    # rows padded to a 16-byte multiple keep the kernel on its 128-bit path
+    vec = 16 // x2.element_size()
+    ldo = (F + vec - 1) // vec * vec if F > 1 else F
+    out_full = torch.empty((csr.n_rows, ldo), dtype=x2.dtype, device=dev)
+    out = out_full[:, :F] if ldo != F else out_full
     if csr.n_rows == 0 or F == 0:
         return out
     if csr.E == 0:
@@ -57,13 +76,13 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
     if heads is None:
         nat.call('pygb_seg_gather_reduce', dev, nat.MEAN if reduce == 'mean' else nat.SUM, dt,
                  nat.ptr(x2), _ld(x2), F, nat.ptr(csr.rowptr), nat.ptr(idx), nat.ptr(w),
-                 nat.ptr(wperm), nat.ptr(bias), csr.n_rows, nat.ptr(out), F)
+                 nat.ptr(wperm), nat.ptr(bias), csr.n_rows, nat.ptr(out), ldo)
     else:
         H, C = heads
         assert H * C == F and reduce == 'sum'
         nat.call('pygb_seg_gather_reduce_heads', dev, dt, nat.ptr(x2), _ld(x2), H, C,
                  nat.ptr(csr.rowptr), nat.ptr(idx), nat.ptr(w), nat.ptr(wperm), nat.ptr(bias),
-                 csr.n_rows, nat.ptr(out), F)
+                 csr.n_rows, nat.ptr(out), ldo)
     return out
 
 
@@ -111,7 +130,7 @@ class _GatherReduce(torch.autograd.Function):
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x if (w is not None and w.requires_grad) else None, w)
         ctx.xshape = shape
-        return out.view((adj.n_dst,) + tuple(shape[1:]))
+        return _unflat(out, adj.n_dst, shape[1:])
 
     @staticmethod
     def backward(ctx, g):
@@ -125,7 +144,7 @@ class _GatherReduce(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             w_t = adj.permuted(_f32(w), 'src') if w is not None else None
             gx = seg_gather_reduce_raw(gs, adj.src, adj.src.col, 'sum', w_t, None, None)
-            gx = gx.view((adj.n_src,) + tuple(ctx.xshape[1:]))
+            gx = _unflat(gx, adj.n_src, ctx.xshape[1:])
         if w is not None and ctx.needs_input_grad[1]:
             ei = adj.edge_index
             gi = gather_rows_raw(gs, ei[adj.i])
@@ -157,7 +176,7 @@ class _GatherRows(torch.autograd.Function):
         (index,) = ctx.saved_tensors
         csr = csr_for(index, ctx.n)
         gx = seg_gather_reduce_raw(g, csr, csr.perm, 'sum')
-        return gx.view(ctx.xshape), None
+        return _unflat(gx, ctx.xshape[0], ctx.xshape[1:]), None
 
 
 def index_select0(x, index):
@@ -185,7 +204,7 @@ class _SegReduce(torch.autograd.Function):
             if name == 'min':
                 out = -out
             ctx.save_for_backward(arg)
-        return out.view((dim_size,) + tail)
+        return _unflat(out, dim_size, tail)
 
     @staticmethod
     def backward(ctx, g):
@@ -247,7 +266,7 @@ class _GatherMax(torch.autograd.Function):
                      adj.n_dst, F, adj.E, nat.ptr(ge), F)
         csr = csr_for(adj.edge_index[adj.j], adj.n_src)
         gx = seg_gather_reduce_raw(ge, csr, csr.perm, 'sum').to(g.dtype)
-        return gx.view(ctx.xshape), None, None
+        return _unflat(gx, ctx.xshape[0], ctx.xshape[1:]), None, None
 
 
 def gather_max(x, adj, zero_below=-10000.0):
