@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define PYGB_ABI_VERSION 1
+#define PYGB_ABI_VERSION 2
 
 enum { PYGB_OK = 0, PYGB_E_ARG = -1, PYGB_E_CUDA = -2, PYGB_E_WORKSPACE = -3,
        PYGB_E_UNSUPPORTED = -4 };
@@ -130,6 +130,36 @@ int pygb_seg_gather_reduce(int reduce, int dtype, const void* x, int64_t ldx,
                            const float* edge_w, const int32_t* wperm,
                            const float* bias, int64_t n_rows, void* out,
                            int64_t ldo, pygb_stream_t s);
+
+/* Streaming form of pygb_seg_gather_reduce (K1 v2; same result contract, weights
+ * must already be in CSR order).  The E slots of the CSR are cut into n_sub
+ * sub-items of Ts slots (pygb_seg_plan picks Ts from E and the SM count); lane
+ * groups of persistent warps stream one sub-item each, staging the gathered rows
+ * through shared memory with cp.async.  Per CSR, pygb_seg_tables builds
+ *   nz_rows[n_rows+2]  the non-empty rows in order, and
+ *   sub_info[n_sub]    rank (in nz_rows) of the row owning slot s*Ts, bit 31 set
+ *                      when that row began in an earlier sub-item;
+ * per index array, pygb_seg_flag_idx makes a copy with bit 31 set on the last
+ * slot of every row (idx = col for the fused gather, perm for a message tensor
+ * in original edge order).  Rows cut by a sub-item boundary are combined from
+ * fp32 partial rows in `ws` in slot order: no atomics, deterministic.  Requires
+ * x/out 16-byte aligned with ldx/ldo padded to a 16-byte multiple >= F.
+ * E = rowptr[n_rows]. */
+int pygb_seg_plan(int64_t E, int32_t* Ts, int64_t* n_sub);
+size_t pygb_seg_tables_workspace(int64_t n_rows);
+int pygb_seg_tables(const int32_t* rowptr, int64_t n_rows, int64_t E, int32_t Ts,
+                    int64_t n_sub, int32_t* nz_rows, int32_t* sub_info, void* ws,
+                    size_t ws_bytes, pygb_stream_t s);
+int pygb_seg_flag_idx(const int32_t* rowptr, int64_t n_rows, const int32_t* idx, int64_t E,
+                      int32_t* idx_flagged, pygb_stream_t s);
+size_t pygb_seg_stream_workspace(int dtype, int64_t n_sub, int64_t F);
+int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t ldx,
+                                  int64_t F, const int32_t* rowptr,
+                                  const int32_t* idx_flagged, const float* edge_w,
+                                  const float* bias, int64_t n_rows, int64_t E,
+                                  const int32_t* nz_rows, const int32_t* sub_info,
+                                  int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
+                                  void* ws, size_t ws_bytes, pygb_stream_t s);
 
 /* Same walk with a per-(edge, head) weight: out[i,h,:] = sum_p
  * head_w[wp(p)*H + h] * x[idx[p],h,:], wp(p) = wperm ? wperm[p] : p — GAT's

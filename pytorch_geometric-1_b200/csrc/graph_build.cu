@@ -106,6 +106,8 @@ __global__ void __launch_bounds__(kThreads) scan_apply(const int* __restrict__ i
   }
 }
 
+}  // namespace
+
 // Exclusive scan in[0..n) -> out[0..n], out[n] = total.  ws_tiles: ceil(n/kTile) ints.
 int exclusive_scan(const int* in, int* out, int64_t n, int* ws_tiles, cudaStream_t st) {
   int64_t nt = ceil_div(n, kTile);
@@ -121,6 +123,10 @@ int exclusive_scan(const int* in, int* out, int64_t n, int* ws_tiles, cudaStream
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }
+
+int64_t exclusive_scan_tiles(int64_t n) { return ceil_div(n > 0 ? n : 1, kTile); }
+
+namespace {
 
 // ---------------------------------------------------------------------------
 // self loops

@@ -1,0 +1,611 @@
+// K1 v2 — streaming segmented gather-reduce (aggr = add | mean).
+//
+// Same result contract as seg_gather_reduce_kernel (seg_reduce.cu), organised
+// for memory-level parallelism and a short instruction stream per edge:
+//
+//  * Work decomposition.  The E slots of the destination-sorted CSR are cut into
+//    sub-items of Ts consecutive slots (equal work whatever the degree skew).  A
+//    warp is 32/LPF independent lane groups; each group streams one sub-item at a
+//    time (LPF lanes x 16 B cover a feature row, VPL vectors per lane), so narrow
+//    rows keep all 32 lanes busy without any cross-group reduction.  Persistent
+//    warps take items w, w+W, ... (an item = EPW consecutive sub-items).
+//
+//  * Row boundaries cost nothing in the hot loop: the index stream carries a flag
+//    in bit 31 ("last slot of its row", pygb_seg_flag_idx) and the row ids come
+//    from nz_rows (the non-empty rows in order), one entry prefetched ahead.
+//    sub_info[s] = rank of the row that owns slot s*Ts | bit 31 if that row began
+//    in an earlier sub-item.  A row cut by a sub-item boundary is reduced
+//    piecewise into fp32 `partial` rows (at most two per sub-item) which the
+//    fix-up kernel adds in slot order: no float atomics, run-to-run
+//    deterministic, and a 17k-edge hub row is spread over ~35 streams.
+//
+//  * Staging.  For each step (one slot per lane group) the warp issues cp.async
+//    (LDGSTS, 16 B per lane, L2-only) copies of the gathered feature rows and a
+//    4-byte copy of the edge weight into a private shared-memory ring of NSTAGE
+//    stages x G steps, NSTAGE-1 stages ahead of the FMAs.  Every lane later reads
+//    exactly the bytes it copied (cp.async.wait_group is the only data sync);
+//    flags and weights cross lanes and are ordered by __syncwarp.  ~8 KB in
+//    flight per warp x 16-20 warps per SM, without spending registers on it.
+//
+// HBM-bound; algorithmic bytes per edge = 4 (col) + 4 (weight) + F*sizeof(T),
+// plus one output row per destination.
+#include <float.h>
+#include <math.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace pygb {
+namespace {
+
+constexpr int kStreamWarps = 4;  // warps per CTA; every warp is an independent stream
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(a));
+  return r;
+}
+__device__ __forceinline__ void sts32(uint32_t a, int v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+template <int G>
+__device__ __forceinline__ void lds_words(uint32_t a, uint32_t* o) {
+  if (G == 4) {
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3])
+                 : "r"(a));
+  } else if (G == 2) {
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(o[0]), "=r"(o[1]) : "r"(a));
+  } else {
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(o[0]) : "r"(a));
+  }
+}
+
+struct StreamParams {
+  const void* x;
+  int64_t ldx;
+  int F;
+  const int* rowptr;
+  const int* idxf;  // index stream with the row-end flag in bit 31
+  const float* ew;
+  const float* bias;
+  int64_t n_rows;
+  int E;
+  int mean;
+  void* out;
+  int64_t ldo;
+  const int* sub_info;
+  const int* nz_rows;
+  int Ts;
+  int n_sub;
+  float* partial;  // [2*n_sub][Fp] fp32
+  int* tail_row;   // [n_sub], pre-set to -1
+  int Fp;
+};
+
+template <typename T, int LPF, int VPL>
+struct StreamCfg {
+  static constexpr int EPW = 32 / LPF;
+  static constexpr int KV = Elem<T>::kVec;
+  static constexpr int NSTAGE = 5;
+  static constexpr int G = VPL >= 4 ? 1 : (VPL >= 2 ? 2 : 4);  // steps per stage
+  static constexpr int DATA_B = VPL * 512;                     // one step
+  static constexpr int META_B = (EPW * G * 4 + 15) / 16 * 16;  // flags, then weights
+  static constexpr int STAGE_B = G * DATA_B + 2 * META_B;
+  static constexpr int WARP_B = NSTAGE * STAGE_B;
+  static constexpr int CTA_B = WARP_B * kStreamWarps;
+};
+
+// Final value of a finished row: mean, bias, conversion, store.
+template <typename T, int KV>
+__device__ __forceinline__ void store_row(float* acc, int f0, int F, float inv_cnt, int mean,
+                                          const float* __restrict__ bias, T* orow) {
+#pragma unroll
+  for (int i = 0; i < KV; ++i) {
+    float r = acc[i];
+    if (mean) r = r * inv_cnt;
+    if (bias && f0 + i < F) r += __ldg(bias + f0 + i);
+    acc[i] = r;
+  }
+  if (f0 + KV <= F) {
+    *reinterpret_cast<uint4*>(orow + f0) = Elem<T>::pack(acc);
+  } else {
+#pragma unroll
+    for (int i = 0; i < KV; ++i)
+      if (f0 + i < F) Elem<T>::store(orow + f0 + i, acc[i]);
+  }
+}
+
+template <int KV>
+__device__ __forceinline__ void store_partial(const float* acc, float* dst) {
+#pragma unroll
+  for (int i = 0; i < KV; i += 4)
+    *reinterpret_cast<float4*>(dst + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
+}
+
+template <typename T, int LPF, int VPL>
+__global__ void __launch_bounds__(kStreamWarps * 32)
+seg_stream_kernel(const StreamParams P) {
+  using C = StreamCfg<T, LPF, VPL>;
+  constexpr int EPW = C::EPW, KV = C::KV, G = C::G, NSTAGE = C::NSTAGE;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int fl = lane & (LPF - 1), es = lane / LPF;
+  const uint32_t sbase =
+      (uint32_t)__cvta_generic_to_shared(smem_raw) + (uint32_t)(warp * C::WARP_B);
+  // per-lane offsets inside a stage
+  const uint32_t data_off = (uint32_t)(lane * 16);
+  const uint32_t flag_off = (uint32_t)(G * C::DATA_B + es * G * 4);
+  const uint32_t w_off = flag_off + C::META_B;
+  const int F = P.F;
+  const int units = (F + KV - 1) / KV;
+  const int W = gridDim.x * kStreamWarps;
+  const char* __restrict__ xb = static_cast<const char*>(P.x) + fl * 16;
+  const uint32_t ldxb = (uint32_t)(P.ldx * sizeof(T));
+  const int* __restrict__ idxf = P.idxf;
+  const float* __restrict__ ew = P.ew;
+  const int* __restrict__ nz_rows = P.nz_rows;
+  const int E = P.E, Ts = P.Ts;
+  const int n_items = (P.n_sub + EPW - 1) / EPW;
+  const int grp_lane0 = es * LPF;
+
+  float acc[VPL][KV];
+#pragma unroll
+  for (int v = 0; v < VPL; ++v)
+#pragma unroll
+    for (int i = 0; i < KV; ++i) acc[v][i] = 0.f;
+
+  for (int item = blockIdx.x + gridDim.x * warp; item < n_items; item += W) {
+    // ---- per lane-group stream state ------------------------------------------------
+    const int s = item * EPW + es;
+    const bool live = s < P.n_sub;
+    const int pg0 = live ? s * Ts : 0;
+    const int n_g = live ? min(Ts, E - pg0) : 0;
+    const int info = live ? __ldg(P.sub_info + s) : 0;
+    int rank = info & 0x7fffffff;
+    bool left_open = info < 0;
+    int row_cur = live ? __ldg(nz_rows + rank) : 0;
+    int row_nxt = live ? __ldg(nz_rows + rank + 1) : 0;
+    int kstart = 0;
+    const int nsteps = __shfl_sync(kFull, n_g, 0);  // group 0 always has the most slots
+    const int nstages = (nsteps + G - 1) / G;
+    const int* __restrict__ my_idx = idxf + pg0 + fl;
+    const float* __restrict__ my_w = ew + pg0;
+    int idx_cur = (fl < n_g) ? __ldg(my_idx) : 0;
+    int idx_nxt = (LPF + fl < n_g) ? __ldg(my_idx + LPF) : 0;
+
+    auto issue_stage = [&](int st) {
+      const uint32_t sb = sbase + (uint32_t)((st % NSTAGE) * C::STAGE_B);
+      const int k0 = st * G;
+      if (st > 0 && (k0 & (LPF - 1)) == 0) {  // next batch of LPF index entries
+        idx_cur = idx_nxt;
+        const int kn = k0 + LPF + fl;
+        idx_nxt = kn < n_g ? __ldg(my_idx + k0 + LPF) : 0;
+      }
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const int k = k0 + g;
+        const int craw = __shfl_sync(kFull, idx_cur, grp_lane0 + (k & (LPF - 1)));
+        if (k < n_g) {
+          const char* src = xb + (uint64_t)(uint32_t)(craw & 0x7fffffff) * ldxb;
+#pragma unroll
+          for (int v = 0; v < VPL; ++v)
+            if (fl + v * LPF < units)
+              cp_async16(sb + (uint32_t)(g * C::DATA_B + v * 512) + data_off, src + v * LPF * 16);
+          if (fl == 0) {
+            sts32(sb + flag_off + g * 4, craw);
+            if (ew != nullptr) cp_async4(sb + w_off + g * 4, my_w + k);
+          }
+        }
+      }
+      cp_async_commit();
+    };
+
+    auto flush = [&](int k) {  // slot k closes the current row of this lane group
+      if (!left_open) {
+        const float inv = 1.f / (float)(k + 1 - kstart);
+        T* orow = static_cast<T*>(P.out) + (int64_t)row_cur * P.ldo;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v)
+          if (fl + v * LPF < units)
+            store_row<T, KV>(acc[v], (fl + v * LPF) * KV, F, inv, P.mean, P.bias, orow);
+      } else {  // the row began in an earlier sub-item: head piece
+        float* pr = P.partial + (int64_t)(2 * s) * P.Fp;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v)
+          if (fl + v * LPF < units) store_partial<KV>(acc[v], pr + (fl + v * LPF) * KV);
+      }
+#pragma unroll
+      for (int v = 0; v < VPL; ++v)
+#pragma unroll
+        for (int i = 0; i < KV; ++i) acc[v][i] = 0.f;
+      left_open = false;
+      kstart = k + 1;
+      ++rank;
+      row_cur = row_nxt;
+      row_nxt = __ldg(nz_rows + rank + 1);
+    };
+
+    auto consume_stage = [&](int st) {
+      const uint32_t sb = sbase + (uint32_t)((st % NSTAGE) * C::STAGE_B);
+      const int k0 = st * G;
+      uint32_t flags[G], wbits[G];
+      lds_words<G>(sb + flag_off, flags);
+      if (ew != nullptr) lds_words<G>(sb + w_off, wbits);
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const int k = k0 + g;
+        if (k < n_g) {
+          const float w = ew != nullptr ? __uint_as_float(wbits[g]) : 1.f;
+#pragma unroll
+          for (int v = 0; v < VPL; ++v) {
+            if (fl + v * LPF < units) {
+              const uint4 qv = lds128(sb + (uint32_t)(g * C::DATA_B + v * 512) + data_off);
+              float f[KV];
+              Elem<T>::unpack(qv, f);
+#pragma unroll
+              for (int i = 0; i < KV; ++i) acc[v][i] = fmaf(w, f[i], acc[v][i]);
+            }
+          }
+          if ((int)flags[g] < 0) flush(k);
+        }
+      }
+    };
+
+    // ---- software pipeline over the stages of this item ------------------------------
+#pragma unroll 1
+    for (int st = 0; st < NSTAGE - 1; ++st) {
+      if (st < nstages) issue_stage(st);
+      else cp_async_commit();
+    }
+#pragma unroll 1
+    for (int st = 0; st < nstages; ++st) {
+      if (st + NSTAGE - 1 < nstages) issue_stage(st + NSTAGE - 1);
+      else cp_async_commit();
+      cp_async_wait<NSTAGE - 1>();
+      __syncwarp();
+      consume_stage(st);
+      __syncwarp();
+    }
+    // ---- a row that continues in the next sub-item: head or tail piece ---------------
+    if (kstart < n_g) {
+      float* pr = P.partial + (int64_t)(2 * s + (left_open ? 0 : 1)) * P.Fp;
+#pragma unroll
+      for (int v = 0; v < VPL; ++v)
+        if (fl + v * LPF < units) store_partial<KV>(acc[v], pr + (fl + v * LPF) * KV);
+      if (fl == 0 && !left_open) P.tail_row[s] = row_cur;
+#pragma unroll
+      for (int v = 0; v < VPL; ++v)
+#pragma unroll
+        for (int i = 0; i < KV; ++i) acc[v][i] = 0.f;
+    }
+  }
+  cp_async_wait<0>();
+}
+
+// Adds the pieces of rows that were cut by sub-item boundaries (slot order), and
+// writes the rows that have no slot at all.
+template <typename T>
+__global__ void __launch_bounds__(256)
+seg_stream_fixup_kernel(const StreamParams P) {
+  constexpr int KV = Elem<T>::kVec;
+  const int lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * 256 + threadIdx.x) >> 5;
+  const int nw = (gridDim.x * 256) >> 5;
+  const int F = P.F, Fp = P.Fp;
+  T* out = static_cast<T*>(P.out);
+  for (int c = gw; c < P.n_sub; c += nw) {
+    const int row = P.tail_row[c];
+    if (row < 0) continue;
+    const int beg = P.rowptr[row], end = P.rowptr[row + 1];
+    const int c_last = (end - 1) / P.Ts;
+    const float inv = 1.f / (float)max(end - beg, 1);
+    for (int f0 = lane * KV; f0 < Fp; f0 += 32 * KV) {
+      float acc[KV];
+      const float* pt = P.partial + (int64_t)(2 * c + 1) * Fp + f0;
+#pragma unroll
+      for (int i = 0; i < KV; ++i) acc[i] = pt[i];
+      for (int cc = c + 1; cc <= c_last; ++cc) {
+        const float* ph = P.partial + (int64_t)(2 * cc) * Fp + f0;
+#pragma unroll
+        for (int i = 0; i < KV; ++i) acc[i] += ph[i];
+      }
+      store_row<T, KV>(acc, f0, F, inv, P.mean, P.bias, out + (int64_t)row * P.ldo);
+    }
+  }
+  // rows without any slot: sum = 0 (+ bias)
+  for (int64_t base = (int64_t)gw * 32; base < P.n_rows; base += (int64_t)nw * 32) {
+    const int64_t row = base + lane;
+    const bool empty = row < P.n_rows && P.rowptr[row] == P.rowptr[row + 1];
+    unsigned mask = __ballot_sync(kFull, empty);
+    while (mask) {
+      const int l = __ffs(mask) - 1;
+      mask &= mask - 1;
+      T* orow = out + (base + l) * P.ldo;
+      for (int f = lane; f < F; f += 32)
+        Elem<T>::store(orow + f, P.bias ? __ldg(P.bias + f) : 0.f);
+    }
+  }
+}
+
+// ---- plan kernels ------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+row_nonempty_kernel(const int* __restrict__ rowptr, int64_t n_rows, int* __restrict__ flag) {
+  for (int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x; r < n_rows;
+       r += (int64_t)gridDim.x * 256)
+    flag[r] = rowptr[r + 1] > rowptr[r];
+}
+
+__global__ void __launch_bounds__(256)
+nz_rows_kernel(const int* __restrict__ rowptr, const int* __restrict__ rank, int64_t n_rows,
+               int* __restrict__ nz_rows) {
+  for (int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x; r < n_rows;
+       r += (int64_t)gridDim.x * 256)
+    if (rowptr[r + 1] > rowptr[r]) nz_rows[rank[r]] = (int)r;
+}
+
+__global__ void __launch_bounds__(256)
+sub_info_kernel(const int* __restrict__ rowptr, const int* __restrict__ rank, int n_rows, int Ts,
+                int n_sub, int* __restrict__ sub_info) {
+  for (int c = blockIdx.x * 256 + threadIdx.x; c < n_sub; c += gridDim.x * 256) {
+    const int target = c * Ts;  // the row r with rowptr[r] <= target < rowptr[r+1]
+    int lo = 0, hi = n_rows;    // invariant: rowptr[lo] <= target < rowptr[hi]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (__ldg(rowptr + mid) <= target) lo = mid;
+      else hi = mid;
+    }
+    sub_info[c] = rank[lo] | (rowptr[lo] < target ? (int)0x80000000 : 0);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+flag_idx_kernel(const int* __restrict__ rowptr, int64_t n_rows, int* __restrict__ idxf) {
+  for (int64_t r = (int64_t)blockIdx.x * 256 + threadIdx.x; r < n_rows;
+       r += (int64_t)gridDim.x * 256) {
+    const int e = rowptr[r + 1];
+    if (e > rowptr[r]) idxf[e - 1] |= (int)0x80000000;
+  }
+}
+
+int sm_count() {
+  static int sms[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (sms[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    sms[dev] = n;
+  }
+  return sms[dev];
+}
+
+inline unsigned grid1d(int64_t n) {
+  int64_t b = ceil_div(n, 256);
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (unsigned)b;
+}
+
+template <typename T, int LPF, int VPL>
+int launch_stream_one(const StreamParams& P, cudaStream_t st) {
+  using C = StreamCfg<T, LPF, VPL>;
+  auto kern = seg_stream_kernel<T, LPF, VPL>;
+  static std::mutex mu;
+  static int ctas_cache[64] = {0};
+  int dev = 0;
+  PYGB_CUDA(cudaGetDevice(&dev));
+  int ctas_per_sm = 0;
+  cudaError_t attr_err = cudaSuccess;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64) ctas_per_sm = ctas_cache[dev];
+    if (ctas_per_sm == 0) {
+      attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::CTA_B);
+      if (attr_err == cudaSuccess)
+        attr_err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, kern,
+                                                                 kStreamWarps * 32, C::CTA_B);
+      if (ctas_per_sm < 1) ctas_per_sm = 1;
+      if (attr_err == cudaSuccess && dev >= 0 && dev < 64) ctas_cache[dev] = ctas_per_sm;
+    }
+  }
+  PYGB_CUDA(attr_err);
+  const int64_t n_items = ceil_div(P.n_sub, C::EPW);
+  int64_t grid = (int64_t)sm_count() * ctas_per_sm;
+  const int64_t need = ceil_div(n_items, kStreamWarps);
+  if (grid > need) grid = need;
+  if (grid < 1) grid = 1;
+  kern<<<(unsigned)grid, kStreamWarps * 32, C::CTA_B, st>>>(P);
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+template <typename T>
+int launch_stream(const StreamParams& P, cudaStream_t st) {
+  constexpr int KV = Elem<T>::kVec;
+  const int units = (P.F + KV - 1) / KV;
+  int rc;
+  if (units <= 4) rc = launch_stream_one<T, 4, 1>(P, st);
+  else if (units <= 8) rc = launch_stream_one<T, 8, 1>(P, st);
+  else if (units <= 16) rc = launch_stream_one<T, 16, 1>(P, st);
+  else if (units <= 32) rc = launch_stream_one<T, 32, 1>(P, st);
+  else if (units <= 64) rc = launch_stream_one<T, 32, 2>(P, st);
+  else if (units <= 96) rc = launch_stream_one<T, 32, 3>(P, st);
+  else rc = launch_stream_one<T, 32, 4>(P, st);
+  if (rc) return rc;
+  int64_t work = (int64_t)P.n_sub * 32;
+  if (work < P.n_rows) work = P.n_rows;
+  seg_stream_fixup_kernel<T><<<grid1d(work), 256, 0, st>>>(P);
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+}  // namespace
+
+int exclusive_scan(const int* in, int* out, int64_t n, int* ws_tiles, cudaStream_t st);
+int64_t exclusive_scan_tiles(int64_t n);
+
+}  // namespace pygb
+
+using namespace pygb;
+
+extern "C" {
+
+int pygb_seg_plan(int64_t E, int32_t* Ts_out, int64_t* n_sub_out) {
+  PYGB_REQUIRE(E >= 0 && E < (1ll << 31) && Ts_out && n_sub_out, "pygb_seg_plan: bad arguments");
+  // >= ~16 sub-items per resident lane-group stream for balance; Ts a power of two in [32, 512]
+  const int64_t streams = (int64_t)sm_count() * 20;
+  int Ts = 512;
+  while (Ts > 32 && E / Ts < streams * 16) Ts >>= 1;
+  *Ts_out = Ts;
+  *n_sub_out = ceil_div(E, Ts);
+  return PYGB_OK;
+}
+
+size_t pygb_seg_tables_workspace(int64_t n_rows) {
+  return 2 * align_up(((size_t)n_rows + 2) * sizeof(int), 256) +
+         align_up(((size_t)exclusive_scan_tiles(n_rows + 1) + 2) * sizeof(int), 256) + 512;
+}
+
+int pygb_seg_tables(const int32_t* rowptr, int64_t n_rows, int64_t E, int32_t Ts, int64_t n_sub,
+                    int32_t* nz_rows, int32_t* sub_info, void* ws, size_t ws_bytes,
+                    pygb_stream_t s) {
+  PYGB_REQUIRE(n_rows >= 0 && E >= 0 && Ts > 0 && n_sub == ceil_div(E, Ts) &&
+                   n_rows < (1ll << 31) - 64 && E < (1ll << 31) - 1024,
+               "pygb_seg_tables: bad arguments");
+  if (n_rows == 0) return PYGB_OK;
+  PYGB_REQUIRE(rowptr && nz_rows && (n_sub == 0 || sub_info), "pygb_seg_tables: null pointer");
+  if (ws_bytes < pygb_seg_tables_workspace(n_rows)) {
+    set_error("pygb_seg_tables: workspace too small");
+    return PYGB_E_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(s);
+  Workspace Wk(ws, ws_bytes);
+  int* flag = Wk.take<int>((size_t)n_rows + 2);
+  int* rank = Wk.take<int>((size_t)n_rows + 2);
+  int* tiles = Wk.take<int>((size_t)exclusive_scan_tiles(n_rows + 1) + 2);
+  row_nonempty_kernel<<<grid1d(n_rows), 256, 0, st>>>(rowptr, n_rows, flag);
+  PYGB_LAUNCH_CHECK();
+  int rc = exclusive_scan(flag, rank, n_rows, tiles, st);
+  if (rc) return rc;
+  // nz_rows has n_rows + 2 entries; the tail past the last non-empty row stays 0
+  PYGB_CUDA(cudaMemsetAsync(nz_rows, 0, ((size_t)n_rows + 2) * sizeof(int), st));
+  nz_rows_kernel<<<grid1d(n_rows), 256, 0, st>>>(rowptr, rank, n_rows, nz_rows);
+  PYGB_LAUNCH_CHECK();
+  if (n_sub > 0) {
+    sub_info_kernel<<<grid1d(n_sub), 256, 0, st>>>(rowptr, rank, (int)n_rows, Ts, (int)n_sub,
+                                                  sub_info);
+    PYGB_LAUNCH_CHECK();
+  }
+  return PYGB_OK;
+}
+
+int pygb_seg_flag_idx(const int32_t* rowptr, int64_t n_rows, const int32_t* idx, int64_t E,
+                      int32_t* idx_flagged, pygb_stream_t s) {
+  PYGB_REQUIRE(n_rows >= 0 && E >= 0, "pygb_seg_flag_idx: bad arguments");
+  if (E == 0 || n_rows == 0) return PYGB_OK;
+  PYGB_REQUIRE(rowptr && idx && idx_flagged, "pygb_seg_flag_idx: null pointer");
+  cudaStream_t st = as_stream(s);
+  if (idx != idx_flagged)
+    PYGB_CUDA(cudaMemcpyAsync(idx_flagged, idx, (size_t)E * sizeof(int), cudaMemcpyDeviceToDevice,
+                              st));
+  flag_idx_kernel<<<grid1d(n_rows), 256, 0, st>>>(rowptr, n_rows, idx_flagged);
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+static int64_t padded_f(int dtype, int64_t F) {
+  const int kv = dtype == PYGB_F32 ? 4 : 8;
+  return (F + kv - 1) / kv * kv;
+}
+
+size_t pygb_seg_stream_workspace(int dtype, int64_t n_sub, int64_t F) {
+  const int64_t fblk = 128 * (dtype == PYGB_F32 ? 4 : 8);
+  if (F > fblk) F = fblk;
+  return align_up((size_t)(2 * n_sub) * padded_f(dtype, F) * sizeof(float), 256) +
+         align_up((size_t)n_sub * sizeof(int), 256) + 256;
+}
+
+int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t ldx, int64_t F,
+                                  const int32_t* rowptr, const int32_t* idx_flagged,
+                                  const float* edge_w, const float* bias, int64_t n_rows,
+                                  int64_t E, const int32_t* nz_rows, const int32_t* sub_info,
+                                  int32_t Ts, int64_t n_sub, void* out, int64_t ldo, void* ws,
+                                  size_t ws_bytes, pygb_stream_t s) {
+  PYGB_REQUIRE(reduce == PYGB_SUM || reduce == PYGB_MEAN,
+               "pygb_seg_gather_reduce_stream: bad reduce %d", reduce);
+  PYGB_REQUIRE(dtype == PYGB_F32 || dtype == PYGB_BF16,
+               "pygb_seg_gather_reduce_stream: bad dtype %d", dtype);
+  PYGB_REQUIRE(F >= 0 && n_rows >= 0 && E >= 0 && E < (1ll << 31) - 1024 &&
+                   n_rows < (1ll << 31) - 64 && ldo >= F && F < (1ll << 24),
+               "pygb_seg_gather_reduce_stream: bad sizes");
+  PYGB_REQUIRE(Ts >= 32 && (Ts & (Ts - 1)) == 0 && n_sub == ceil_div(E, Ts),
+               "pygb_seg_gather_reduce_stream: bad plan (Ts must be a power of two >= 32)");
+  if (n_rows == 0 || F == 0) return PYGB_OK;
+  PYGB_REQUIRE(rowptr && out && (E == 0 || (x && idx_flagged && nz_rows && sub_info)),
+               "pygb_seg_gather_reduce_stream: null pointer");
+  const int esz = dtype == PYGB_F32 ? 4 : 2;
+  const int kv = 16 / esz;
+  PYGB_REQUIRE(aligned16(x) && aligned16(out) && ldx % kv == 0 && ldo % kv == 0 &&
+                   ldx >= padded_f(dtype, F) && ldo >= padded_f(dtype, F) &&
+                   ldx * esz < (1ll << 31),
+               "pygb_seg_gather_reduce_stream: x/out rows must be 16-byte aligned and padded");
+  if (ws_bytes < pygb_seg_stream_workspace(dtype, n_sub, F)) {
+    set_error("pygb_seg_gather_reduce_stream: workspace too small");
+    return PYGB_E_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(s);
+  // feature blocks of at most 128 16-byte units (2 KB) per row
+  const int64_t fblk = 128 * kv;
+  const int64_t Fp_max = padded_f(dtype, F < fblk ? F : fblk);
+  Workspace Wk(ws, ws_bytes);
+  float* partial = Wk.take<float>((size_t)(2 * n_sub) * Fp_max);
+  int* tail_row = Wk.take<int>((size_t)n_sub);
+  for (int64_t f0 = 0; f0 < F; f0 += fblk) {
+    const int64_t fb = F - f0 < fblk ? F - f0 : fblk;
+    StreamParams P;
+    P.x = static_cast<const char*>(x) + f0 * esz;
+    P.ldx = ldx;
+    P.F = (int)fb;
+    P.rowptr = rowptr;
+    P.idxf = idx_flagged;
+    P.ew = edge_w;
+    P.bias = bias ? bias + f0 : nullptr;
+    P.n_rows = n_rows;
+    P.E = (int)E;
+    P.mean = reduce == PYGB_MEAN;
+    P.out = static_cast<char*>(out) + f0 * esz;
+    P.ldo = ldo;
+    P.sub_info = sub_info;
+    P.nz_rows = nz_rows;
+    P.Ts = Ts;
+    P.n_sub = (int)n_sub;
+    P.partial = partial;
+    P.tail_row = tail_row;
+    P.Fp = (int)padded_f(dtype, fb);
+    if (n_sub > 0) PYGB_CUDA(cudaMemsetAsync(tail_row, 0xff, (size_t)n_sub * sizeof(int), st));
+    int rc = dtype == PYGB_F32 ? launch_stream<float>(P, st) : launch_stream<__nv_bfloat16>(P, st);
+    if (rc) return rc;
+  }
+  return PYGB_OK;
+}
+
+}  // extern "C"

@@ -35,6 +35,13 @@ SIGNATURES = {
     'pygb_weighted_degree': (_I, [_P, _P, _P, _L, _P, _P]),
     'pygb_gcn_norm': (_I, [_P, _P, _L, _L, _P, _P, _P]),
     'pygb_seg_gather_reduce': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
+    'pygb_seg_plan': (_I, [_L, _P, _P]),
+    'pygb_seg_tables_workspace': (_Z, [_L]),
+    'pygb_seg_tables': (_I, [_P, _L, _L, _I, _L, _P, _P, _P, _Z, _P]),
+    'pygb_seg_flag_idx': (_I, [_P, _L, _P, _L, _P, _P]),
+    'pygb_seg_stream_workspace': (_Z, [_I, _L, _L]),
+    'pygb_seg_gather_reduce_stream': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P, _I,
+                                           _L, _P, _L, _P, _Z, _P]),
     'pygb_seg_gather_reduce_heads': (_I, [_I, _P, _L, _I, _I, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
     'pygb_gather_rows': (_I, [_I, _P, _L, _L, _P, _L, _P, _L, _P]),
     'pygb_seg_max': (_I, [_I, _P, _L, _L, _P, _P, _P, _L, _L, _F, _I, _P, _L, _P, _P]),
@@ -79,7 +86,7 @@ def load():
             fn = getattr(lib, name)
             fn.restype = res
             fn.argtypes = args
-        if lib.pygb_abi_version() != 1:
+        if lib.pygb_abi_version() != 2:
             raise NativeError('libpygb.so ABI version mismatch')
         _lib = lib
     return _lib

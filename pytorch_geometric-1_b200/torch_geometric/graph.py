@@ -13,6 +13,7 @@ version counter), so ``GATConv`` — which the reference rebuilds every forward 
 and the generic ``scatter_`` path sort once per graph.
 """
 import collections
+import ctypes
 import threading
 
 import torch
@@ -21,12 +22,58 @@ from . import _native as nat
 
 
 class CSR(object):
-    __slots__ = ('rowptr', 'col', 'perm', 'n_rows', 'n_cols', 'E', '_keep')
+    __slots__ = ('rowptr', 'col', 'perm', 'n_rows', 'n_cols', 'E', '_keep', '_items')
 
     def __init__(self, rowptr, col, perm, n_rows, n_cols, E, keep=None):
         self.rowptr, self.col, self.perm = rowptr, col, perm
         self.n_rows, self.n_cols, self.E = n_rows, n_cols, E
         self._keep = keep
+        self._items = {}
+
+    def items(self, T=None):
+        """Work decomposition of the streaming kernels: ``(Ts, n_sub, nz_rows,
+        sub_info)`` (see include/pygb.h, pygb_seg_tables); built once, cached.
+        ``T=None`` lets the library choose Ts from E and the SM count."""
+        hit = self._items.get(T)
+        if hit is not None:
+            return hit
+        dev = self.rowptr.device
+        if T is None:
+            t, n = ctypes.c_int32(0), ctypes.c_int64(0)
+            with torch.cuda.device(dev):
+                rc = nat.load().pygb_seg_plan(self.E, ctypes.byref(t), ctypes.byref(n))
+            if rc != 0:
+                raise nat.NativeError(nat.load().pygb_last_error().decode())
+            t, n = int(t.value), int(n.value)
+        else:
+            t, n = int(T), (self.E + int(T) - 1) // int(T)
+        nz_rows = torch.empty(self.n_rows + 2, dtype=torch.int32, device=dev)
+        sub_info = torch.empty(max(n, 1), dtype=torch.int32, device=dev)
+        if self.n_rows > 0:
+            ws_bytes = nat.workspace('pygb_seg_tables_workspace', self.n_rows)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            nat.call('pygb_seg_tables', dev, nat.ptr(self.rowptr), self.n_rows, self.E, t, n,
+                     nat.ptr(nz_rows), nat.ptr(sub_info), nat.ptr(ws), ws_bytes)
+        plan = (t, n, nz_rows, sub_info)
+        self._items[T] = plan
+        if T is None:
+            self._items[t] = plan
+        return plan
+
+    def flagged(self, which):
+        """``col`` or ``perm`` with bit 31 set on the last slot of every row (the
+        index stream of the streaming kernels); built once, cached."""
+        key = ('flag', which)
+        hit = self._items.get(key)
+        if hit is not None:
+            return hit
+        idx = self.col if which == 'col' else self.perm
+        out = torch.empty_like(idx)
+        if self.E > 0:
+            nat.call('pygb_seg_flag_idx', idx.device, nat.ptr(self.rowptr), self.n_rows,
+                     nat.ptr(idx), self.E, nat.ptr(out))
+        self._items[key] = out
+        return out
 
     @property
     def device(self):

@@ -10,6 +10,10 @@ from . import _native as nat
 from .graph import adj_for, csr_for  # noqa: F401  (re-exported)
 
 NEG_INF = float('-inf')
+# K1 routing: the streaming kernel (seg_stream.cu) when the rows are 16-byte aligned and
+# padded, else the one-warp-per-row kernel.  STREAM_T forces the item size (tests).
+STREAM = True
+STREAM_T = None
 
 
 def _rows2d(x):
@@ -73,9 +77,26 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
     dt = nat.dtype_code(x2)
     w = _f32(w)
     bias = _f32(bias)
-    if heads is None:
+    ldx = _ld(x2)
+    if (heads is None and wperm is None and STREAM and F > 1 and x2.data_ptr() % 16 == 0
+            and ldx % vec == 0 and ldx >= ldo):
+        # K1 v2: streaming kernel over equal-slot work items
+        Ts, n_sub, nz_rows, sub_info = csr.items(STREAM_T)
+        if idx is csr.col:
+            idxf = csr.flagged('col')
+        elif idx is csr.perm:
+            idxf = csr.flagged('perm')
+        else:
+            raise ValueError('seg_gather_reduce_raw: idx must be csr.col or csr.perm')
+        ws_bytes = nat.workspace('pygb_seg_stream_workspace', dt, n_sub, F)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        nat.call('pygb_seg_gather_reduce_stream', dev, nat.MEAN if reduce == 'mean' else nat.SUM,
+                 dt, nat.ptr(x2), ldx, F, nat.ptr(csr.rowptr), nat.ptr(idxf), nat.ptr(w),
+                 nat.ptr(bias), csr.n_rows, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub,
+                 nat.ptr(out), ldo, nat.ptr(ws), ws_bytes)
+    elif heads is None:
         nat.call('pygb_seg_gather_reduce', dev, nat.MEAN if reduce == 'mean' else nat.SUM, dt,
-                 nat.ptr(x2), _ld(x2), F, nat.ptr(csr.rowptr), nat.ptr(idx), nat.ptr(w),
+                 nat.ptr(x2), ldx, F, nat.ptr(csr.rowptr), nat.ptr(idx), nat.ptr(w),
                  nat.ptr(wperm), nat.ptr(bias), csr.n_rows, nat.ptr(out), ldo)
     else:
         H, C = heads

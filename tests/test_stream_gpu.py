@@ -1,0 +1,79 @@
+"""GPU: the streaming K1 (seg_stream.cu) against the oracle and against the
+one-warp-per-row kernel, with the item size forced small so that rows are cut by
+item boundaries (partial rows + fix-up), plus empty rows and hub rows."""
+import pytest
+import torch
+
+from oracle import ref_cpu as O
+from util import assert_close, skewed_graph
+
+pytestmark = pytest.mark.gpu
+
+
+def _feat(n, F, seed, dtype=torch.float32):
+    return torch.randn(n, F, generator=torch.Generator().manual_seed(seed)).to(dtype)
+
+
+@pytest.fixture
+def ops_mod():
+    from torch_geometric import ops
+    old = (ops.STREAM, ops.STREAM_T)
+    yield ops
+    ops.STREAM, ops.STREAM_T = old
+
+
+@pytest.mark.parametrize('T', [32, 64, 512, None])
+@pytest.mark.parametrize('F', [2, 4, 7, 16, 47, 64, 100, 128, 256, 300, 512, 700, 1100])
+def test_stream_matches_oracle_and_v1(dev, ops_mod, F, T):
+    from torch_geometric.utils import scatter_
+    ops = ops_mod
+    n, E = 900, 12000
+    idx = skewed_graph(n, E, F + 3)[1]           # hubs of ~1200 slots, upper half of rows empty
+    src = _feat(E, F, 1)
+    for name in ('add', 'mean'):
+        ref = O.scatter_(name, src, idx, 0, n)
+        ops.STREAM, ops.STREAM_T = True, T
+        got = scatter_(name, src.to(dev), idx.to(dev), 0, n)
+        again = scatter_(name, src.to(dev), idx.to(dev), 0, n)
+        ops.STREAM = False
+        v1 = scatter_(name, src.to(dev), idx.to(dev), 0, n)
+        assert_close(got, ref, 1e-5, name)
+        assert_close(got, v1, 1e-5, name + ' vs v1')
+        assert torch.equal(got, again), 'not deterministic'
+
+
+@pytest.mark.parametrize('T', [32, None])
+@pytest.mark.parametrize('dtype,tol', [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+def test_stream_weighted_gather(dev, ops_mod, dtype, tol, T):
+    """Fused norm * x_j gather-reduce with bias (the GCNConv route)."""
+    from torch_geometric.graph import Adj
+    ops = ops_mod
+    n, E, F = 500, 9000, 96
+    ei = skewed_graph(n, E, 5)
+    x = _feat(n, F, 2)
+    w = torch.rand(E, generator=torch.Generator().manual_seed(3))
+    bias = _feat(1, F, 4).view(-1)
+    ref = torch.zeros(n, F).index_add_(0, ei[1], w.view(-1, 1) * x.to(dtype).float()[ei[0]]) + bias
+    ops.STREAM, ops.STREAM_T = True, T
+    adj = Adj(ei.to(dev), 1, (n, n))
+    got = ops.gather_reduce(x.to(dev).to(dtype), adj, w.to(dev), 'sum', bias.to(dev))
+    assert got.dtype == dtype
+    assert_close(got.float(), ref, tol, 'weighted gather')
+
+
+def test_stream_single_giant_row_and_all_empty(dev, ops_mod):
+    from torch_geometric.utils import scatter_
+    ops = ops_mod
+    ops.STREAM, ops.STREAM_T = True, 64
+    idx1 = torch.zeros(40000, dtype=torch.long)
+    big = _feat(40000, 8, 3)
+    assert_close(scatter_('add', big.to(dev), idx1.to(dev), 0, 3), O.scatter_('add', big, idx1, 0, 3), 2e-5)
+    assert_close(scatter_('mean', big.to(dev), idx1.to(dev), 0, 3), O.scatter_('mean', big, idx1, 0, 3), 2e-5)
+    # only the last row is populated; long runs of empty rows before it
+    idx2 = torch.full((300,), 4999, dtype=torch.long)
+    s2 = _feat(300, 12, 5)
+    assert_close(scatter_('add', s2.to(dev), idx2.to(dev), 0, 5000), O.scatter_('add', s2, idx2, 0, 5000))
+    # sparse rows: every 70th row has one entry (runs of > 64 empty rows inside an item)
+    idx3 = torch.arange(0, 7000, 70)
+    s3 = _feat(100, 20, 6)
+    assert_close(scatter_('add', s3.to(dev), idx3.to(dev), 0, 7000), O.scatter_('add', s3, idx3, 0, 7000))
