@@ -301,11 +301,12 @@ def run_b200(args):
     value = 3.0 * e_prime / (ms_per_step * 1e-3)
 
     # ---- roofline of the dominant kernel: K1 at F = hidden ---------------------
+    K1_NAMES = ('pygb_seg_gather_reduce', 'pygb_seg_gather_reduce_stream')
     k1 = [(e0.elapsed_time(e1), a) for (name, a, e0, e1) in log
-          if name == 'pygb_seg_gather_reduce' and a[4] == hid]
+          if name in K1_NAMES and a[4] == hid]
     k1_ms = sum(t for t, _ in k1) / max(len(k1), 1)
     all_k1_ms = sum(e0.elapsed_time(e1) for (name, a, e0, e1) in log
-                    if name == 'pygb_seg_gather_reduce') / args.steps
+                    if name in K1_NAMES) / args.steps
     e_local = e_prime if world == 1 else graph.num_edges_local
     bytes_k1 = k1_bytes(e_local, n_rows_local, hid, itemsize)
     peak, peak_src = peaks()
@@ -317,7 +318,7 @@ def run_b200(args):
             traffic = json.load(open(tpath)).get(args.dtype)
         except Exception:
             traffic = None
-    roofline = {'bound': 'hbm', 'kernel': 'seg_gather_reduce_kernel (K1), F=%d %s' % (hid, args.dtype),
+    roofline = {'bound': 'hbm', 'kernel': 'seg_stream_kernel + fixup (K1 v2), F=%d %s' % (hid, args.dtype),
                 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                 'frac_of_nominal_8000': achieved / 8000.0, 'peak_source': peak_src,
                 'algorithmic_bytes_per_launch': bytes_k1, 'avg_launch_ms': k1_ms,

@@ -33,6 +33,7 @@
 #include <math.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -103,7 +104,7 @@ template <typename T, int LPF, int VPL>
 struct StreamCfg {
   static constexpr int EPW = 32 / LPF;
   static constexpr int KV = Elem<T>::kVec;
-  static constexpr int NSTAGE = 5;
+  static constexpr int NSTAGE = 4;                             // power of two
   static constexpr int G = VPL >= 4 ? 1 : (VPL >= 2 ? 2 : 4);  // steps per stage
   static constexpr int DATA_B = VPL * 512;                     // one step
   static constexpr int META_B = (EPW * G * 4 + 15) / 16 * 16;  // flags, then weights
@@ -139,7 +140,27 @@ __device__ __forceinline__ void store_partial(const float* acc, float* dst) {
     *reinterpret_cast<float4*>(dst + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
 }
 
-template <typename T, int LPF, int VPL>
+template <int G>
+__device__ __forceinline__ void sts_words(uint32_t a, const int* v) {
+  if (G == 4) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3])
+                 : "memory");
+  } else if (G == 2) {
+    asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(a), "r"(v[0]), "r"(v[1]) : "memory");
+  } else {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v[0]) : "memory");
+  }
+}
+template <int BYTES>
+__device__ __forceinline__ void cp_async_small(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(dst), "l"(src), "n"(BYTES)
+               : "memory");
+}
+
+// WEIGHTED: an edge weight stream exists (16-byte aligned).  EXACT: a feature row
+// is exactly LPF*VPL 16-byte units, so no lane is idle and no unit test is needed.
+template <typename T, int LPF, int VPL, bool WEIGHTED, bool EXACT>
 __global__ void __launch_bounds__(kStreamWarps * 32)
 seg_stream_kernel(const StreamParams P) {
   using C = StreamCfg<T, LPF, VPL>;
@@ -147,16 +168,18 @@ seg_stream_kernel(const StreamParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int fl = lane & (LPF - 1), es = lane / LPF;
-  const uint32_t sbase =
-      (uint32_t)__cvta_generic_to_shared(smem_raw) + (uint32_t)(warp * C::WARP_B);
-  // per-lane offsets inside a stage
-  const uint32_t data_off = (uint32_t)(lane * 16);
-  const uint32_t flag_off = (uint32_t)(G * C::DATA_B + es * G * 4);
-  const uint32_t w_off = flag_off + C::META_B;
+  // per-lane base inside a stage: data at +0, flags at flag_off, weights after them
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem_raw) +
+                         (uint32_t)(warp * C::WARP_B) + (uint32_t)(lane * 16);
+  const uint32_t meta = (uint32_t)(G * C::DATA_B + es * G * 4) - (uint32_t)(lane * 16);
   const int F = P.F;
   const int units = (F + KV - 1) / KV;
+  bool act[VPL];
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) act[v] = EXACT || (fl + v * LPF < units);
   const int W = gridDim.x * kStreamWarps;
-  const char* __restrict__ xb = static_cast<const char*>(P.x) + fl * 16;
+  const char* xb = static_cast<const char*>(P.x) + fl * 16;
+  asm volatile("" : "+l"(xb));  // keep the per-lane base in registers
   const uint32_t ldxb = (uint32_t)(P.ldx * sizeof(T));
   const int* __restrict__ idxf = P.idxf;
   const float* __restrict__ ew = P.ew;
@@ -164,6 +187,7 @@ seg_stream_kernel(const StreamParams P) {
   const int E = P.E, Ts = P.Ts;
   const int n_items = (P.n_sub + EPW - 1) / EPW;
   const int grp_lane0 = es * LPF;
+  const bool lead = fl == 0;
 
   float acc[VPL][KV];
 #pragma unroll
@@ -183,39 +207,12 @@ seg_stream_kernel(const StreamParams P) {
     int row_cur = live ? __ldg(nz_rows + rank) : 0;
     int row_nxt = live ? __ldg(nz_rows + rank + 1) : 0;
     int kstart = 0;
-    const int nsteps = __shfl_sync(kFull, n_g, 0);  // group 0 always has the most slots
-    const int nstages = (nsteps + G - 1) / G;
     const int* __restrict__ my_idx = idxf + pg0 + fl;
     const float* __restrict__ my_w = ew + pg0;
     int idx_cur = (fl < n_g) ? __ldg(my_idx) : 0;
     int idx_nxt = (LPF + fl < n_g) ? __ldg(my_idx + LPF) : 0;
-
-    auto issue_stage = [&](int st) {
-      const uint32_t sb = sbase + (uint32_t)((st % NSTAGE) * C::STAGE_B);
-      const int k0 = st * G;
-      if (st > 0 && (k0 & (LPF - 1)) == 0) {  // next batch of LPF index entries
-        idx_cur = idx_nxt;
-        const int kn = k0 + LPF + fl;
-        idx_nxt = kn < n_g ? __ldg(my_idx + k0 + LPF) : 0;
-      }
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        const int k = k0 + g;
-        const int craw = __shfl_sync(kFull, idx_cur, grp_lane0 + (k & (LPF - 1)));
-        if (k < n_g) {
-          const char* src = xb + (uint64_t)(uint32_t)(craw & 0x7fffffff) * ldxb;
-#pragma unroll
-          for (int v = 0; v < VPL; ++v)
-            if (fl + v * LPF < units)
-              cp_async16(sb + (uint32_t)(g * C::DATA_B + v * 512) + data_off, src + v * LPF * 16);
-          if (fl == 0) {
-            sts32(sb + flag_off + g * 4, craw);
-            if (ew != nullptr) cp_async4(sb + w_off + g * 4, my_w + k);
-          }
-        }
-      }
-      cp_async_commit();
-    };
+    // every lane group of the warp has all Ts slots (true except at the very end of the CSR)
+    const bool all_full = (int64_t)(item * EPW + EPW) * Ts <= (int64_t)E;
 
     auto flush = [&](int k) {  // slot k closes the current row of this lane group
       if (!left_open) {
@@ -223,13 +220,12 @@ seg_stream_kernel(const StreamParams P) {
         T* orow = static_cast<T*>(P.out) + (int64_t)row_cur * P.ldo;
 #pragma unroll
         for (int v = 0; v < VPL; ++v)
-          if (fl + v * LPF < units)
-            store_row<T, KV>(acc[v], (fl + v * LPF) * KV, F, inv, P.mean, P.bias, orow);
+          if (act[v]) store_row<T, KV>(acc[v], (fl + v * LPF) * KV, F, inv, P.mean, P.bias, orow);
       } else {  // the row began in an earlier sub-item: head piece
         float* pr = P.partial + (int64_t)(2 * s) * P.Fp;
 #pragma unroll
         for (int v = 0; v < VPL; ++v)
-          if (fl + v * LPF < units) store_partial<KV>(acc[v], pr + (fl + v * LPF) * KV);
+          if (act[v]) store_partial<KV>(acc[v], pr + (fl + v * LPF) * KV);
       }
 #pragma unroll
       for (int v = 0; v < VPL; ++v)
@@ -242,54 +238,100 @@ seg_stream_kernel(const StreamParams P) {
       row_nxt = __ldg(nz_rows + rank + 1);
     };
 
-    auto consume_stage = [&](int st) {
-      const uint32_t sb = sbase + (uint32_t)((st % NSTAGE) * C::STAGE_B);
-      const int k0 = st * G;
-      uint32_t flags[G], wbits[G];
-      lds_words<G>(sb + flag_off, flags);
-      if (ew != nullptr) lds_words<G>(sb + w_off, wbits);
+    auto run = [&](auto full_tag) {
+      constexpr bool FULL = decltype(full_tag)::value;
+      const int nsteps = FULL ? Ts : __shfl_sync(kFull, n_g, 0);  // group 0 has the most slots
+      const int nstages = (nsteps + G - 1) / G;
+
+      auto issue_stage = [&](int st) {
+        const uint32_t sb = sbase + (uint32_t)((st & (NSTAGE - 1)) * C::STAGE_B);
+        const int k0 = st * G;
+        if (st > 0 && (k0 & (LPF - 1)) == 0) {  // next batch of LPF index entries
+          idx_cur = idx_nxt;
+          idx_nxt = (FULL ? k0 + LPF < Ts : k0 + LPF + fl < n_g) ? __ldg(my_idx + k0 + LPF) : 0;
+        }
+        int craw[G];
+        const char* src[G];
+        const int lane0 = grp_lane0 + (k0 & (LPF - 1));
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
-        const int k = k0 + g;
-        if (k < n_g) {
-          const float w = ew != nullptr ? __uint_as_float(wbits[g]) : 1.f;
+        for (int g = 0; g < G; ++g) {
+          craw[g] = __shfl_sync(kFull, idx_cur, lane0 + g);
+          src[g] = xb + (uint64_t)(uint32_t)(craw[g] & 0x7fffffff) * ldxb;
+        }
 #pragma unroll
-          for (int v = 0; v < VPL; ++v) {
-            if (fl + v * LPF < units) {
-              const uint4 qv = lds128(sb + (uint32_t)(g * C::DATA_B + v * 512) + data_off);
-              float f[KV];
-              Elem<T>::unpack(qv, f);
+        for (int g = 0; g < G; ++g) {
+          if (FULL || k0 + g < n_g) {
 #pragma unroll
-              for (int i = 0; i < KV; ++i) acc[v][i] = fmaf(w, f[i], acc[v][i]);
+            for (int v = 0; v < VPL; ++v)
+              if (act[v])
+                cp_async16(sb + (uint32_t)(g * C::DATA_B + v * 512), src[g] + v * LPF * 16);
+          }
+        }
+        if (lead) {
+          sts_words<G>(sb + meta, craw);
+          if (WEIGHTED) {
+            if (FULL) {
+              cp_async_small<G * 4>(sb + meta + C::META_B, my_w + k0);
+            } else {
+#pragma unroll
+              for (int g = 0; g < G; ++g)
+                if (k0 + g < n_g) cp_async_small<4>(sb + meta + C::META_B + g * 4, my_w + k0 + g);
             }
           }
-          if ((int)flags[g] < 0) flush(k);
         }
+        cp_async_commit();
+      };
+
+      auto consume_stage = [&](int st) {
+        const uint32_t sb = sbase + (uint32_t)((st & (NSTAGE - 1)) * C::STAGE_B);
+        const int k0 = st * G;
+        uint32_t flags[G], wbits[G];
+        lds_words<G>(sb + meta, flags);
+        if (WEIGHTED) lds_words<G>(sb + meta + C::META_B, wbits);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          if (FULL || k0 + g < n_g) {
+            const float w = WEIGHTED ? __uint_as_float(wbits[g]) : 1.f;
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) {
+              if (act[v]) {
+                const uint4 qv = lds128(sb + (uint32_t)(g * C::DATA_B + v * 512));
+                float f[KV];
+                Elem<T>::unpack(qv, f);
+#pragma unroll
+                for (int i = 0; i < KV; ++i) acc[v][i] = fmaf(w, f[i], acc[v][i]);
+              }
+            }
+            if ((int)flags[g] < 0) flush(k0 + g);
+          }
+        }
+      };
+
+#pragma unroll 1
+      for (int st = 0; st < NSTAGE - 1; ++st) {
+        if (st < nstages) issue_stage(st);
+        else cp_async_commit();
+      }
+#pragma unroll 1
+      for (int st = 0; st < nstages; ++st) {
+        if (st + NSTAGE - 1 < nstages) issue_stage(st + NSTAGE - 1);
+        else cp_async_commit();
+        cp_async_wait<NSTAGE - 1>();
+        __syncwarp();
+        consume_stage(st);
+        __syncwarp();
       }
     };
+    if (all_full) run(std::true_type{});
+    else run(std::false_type{});
 
-    // ---- software pipeline over the stages of this item ------------------------------
-#pragma unroll 1
-    for (int st = 0; st < NSTAGE - 1; ++st) {
-      if (st < nstages) issue_stage(st);
-      else cp_async_commit();
-    }
-#pragma unroll 1
-    for (int st = 0; st < nstages; ++st) {
-      if (st + NSTAGE - 1 < nstages) issue_stage(st + NSTAGE - 1);
-      else cp_async_commit();
-      cp_async_wait<NSTAGE - 1>();
-      __syncwarp();
-      consume_stage(st);
-      __syncwarp();
-    }
     // ---- a row that continues in the next sub-item: head or tail piece ---------------
     if (kstart < n_g) {
       float* pr = P.partial + (int64_t)(2 * s + (left_open ? 0 : 1)) * P.Fp;
 #pragma unroll
       for (int v = 0; v < VPL; ++v)
-        if (fl + v * LPF < units) store_partial<KV>(acc[v], pr + (fl + v * LPF) * KV);
-      if (fl == 0 && !left_open) P.tail_row[s] = row_cur;
+        if (act[v]) store_partial<KV>(acc[v], pr + (fl + v * LPF) * KV);
+      if (lead && !left_open) P.tail_row[s] = row_cur;
 #pragma unroll
       for (int v = 0; v < VPL; ++v)
 #pragma unroll
@@ -405,10 +447,10 @@ inline unsigned grid1d(int64_t n) {
   return (unsigned)b;
 }
 
-template <typename T, int LPF, int VPL>
-int launch_stream_one(const StreamParams& P, cudaStream_t st) {
+template <typename T, int LPF, int VPL, bool WEIGHTED, bool EXACT>
+int launch_stream_k(const StreamParams& P, cudaStream_t st) {
   using C = StreamCfg<T, LPF, VPL>;
-  auto kern = seg_stream_kernel<T, LPF, VPL>;
+  auto kern = seg_stream_kernel<T, LPF, VPL, WEIGHTED, EXACT>;
   static std::mutex mu;
   static int ctas_cache[64] = {0};
   int dev = 0;
@@ -436,6 +478,17 @@ int launch_stream_one(const StreamParams& P, cudaStream_t st) {
   kern<<<(unsigned)grid, kStreamWarps * 32, C::CTA_B, st>>>(P);
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
+}
+
+template <typename T, int LPF, int VPL>
+int launch_stream_one(const StreamParams& P, cudaStream_t st) {
+  constexpr int KV = Elem<T>::kVec;
+  const bool exact = (P.F % KV == 0) && (P.F / KV == LPF * VPL);
+  if (P.ew != nullptr)
+    return exact ? launch_stream_k<T, LPF, VPL, true, true>(P, st)
+                 : launch_stream_k<T, LPF, VPL, true, false>(P, st);
+  return exact ? launch_stream_k<T, LPF, VPL, false, true>(P, st)
+               : launch_stream_k<T, LPF, VPL, false, false>(P, st);
 }
 
 template <typename T>
@@ -566,8 +619,9 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
   const int kv = 16 / esz;
   PYGB_REQUIRE(aligned16(x) && aligned16(out) && ldx % kv == 0 && ldo % kv == 0 &&
                    ldx >= padded_f(dtype, F) && ldo >= padded_f(dtype, F) &&
-                   ldx * esz < (1ll << 31),
-               "pygb_seg_gather_reduce_stream: x/out rows must be 16-byte aligned and padded");
+                   ldx * esz < (1ll << 31) && aligned16(edge_w),
+               "pygb_seg_gather_reduce_stream: x/out rows (and edge_w) must be 16-byte aligned, "
+               "rows padded to 16 bytes");
   if (ws_bytes < pygb_seg_stream_workspace(dtype, n_sub, F)) {
     set_error("pygb_seg_gather_reduce_stream: workspace too small");
     return PYGB_E_WORKSPACE;

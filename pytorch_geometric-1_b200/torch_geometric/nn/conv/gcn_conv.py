@@ -75,17 +75,33 @@ class GCNConv(MessagePassing):
             norm = norm.to(dtype)
         return edge_index, norm
 
+    def _aggregate_first(self, x):
+        """``A (X W) = (A X) W``: aggregate at the narrower of the two widths.  Only
+        for the stock message/update on 2-D inputs whose rows are already 16-byte
+        multiples (the 128-bit gather path); sums differ from the other order by
+        fp32 rounding only (~1e-7 relative)."""
+        cls = type(self)
+        if (cls.message is not GCNConv.message or cls.update is not GCNConv.update
+                or self.node_dim != 0 or not torch.is_tensor(x) or x.dim() != 2):
+            return False
+        if x.dtype not in (torch.float32, torch.bfloat16) or not x.is_cuda:
+            return False
+        vec = 16 // x.element_size()
+        return self.in_channels < self.out_channels and self.in_channels % vec == 0
+
     def forward(self, x, edge_index, edge_weight=None):
         """"""
-        # X·W with the output row padded to 16 bytes so that the aggregation stays on
-        # its 128-bit load path for widths like 7 or 47 (the padding is sliced away).
-        vec = 16 // x.element_size() if x.is_floating_point() else 1
-        pad = (-self.out_channels) % vec if self.out_channels > 1 else 0
-        if pad and x.dim() == 2:
-            w = torch.nn.functional.pad(self.weight, (0, pad))
-            x = torch.matmul(x, w)[:, :self.out_channels]
-        else:
-            x = torch.matmul(x, self.weight)
+        agg_first = self._aggregate_first(x)
+        if not agg_first:
+            # X·W with the output row padded to 16 bytes so that the aggregation stays on
+            # its 128-bit load path for widths like 7 or 47 (the padding is sliced away).
+            vec = 16 // x.element_size() if x.is_floating_point() else 1
+            pad = (-self.out_channels) % vec if self.out_channels > 1 else 0
+            if pad and x.dim() == 2:
+                w = torch.nn.functional.pad(self.weight, (0, pad))
+                x = torch.matmul(x, w)[:, :self.out_channels]
+            else:
+                x = torch.matmul(x, self.weight)
 
         if self.cached and self.cached_result is not None:
             if edge_index.size(1) != self.cached_num_edges:
@@ -106,6 +122,15 @@ class GCNConv(MessagePassing):
 
         edge_index, norm = self.cached_result
 
+        if agg_first:
+            self._defer_bias = True
+            try:
+                h = self.propagate(edge_index, x=x, norm=norm)
+            finally:
+                self._defer_bias = False
+            if self.bias is not None:
+                return torch.addmm(self.bias, h, self.weight)
+            return torch.matmul(h, self.weight)
         return self.propagate(edge_index, x=x, norm=norm)
 
     def _fused_propagate(self, edge_index, size, i, kwargs):
@@ -117,8 +142,9 @@ class GCNConv(MessagePassing):
         if not torch.is_tensor(x) or x.dtype not in (torch.float32, torch.bfloat16):
             return NotImplemented
         adj = adj_for(edge_index, i, size)
-        out = ops.gather_reduce(x, adj, norm, 'sum', self.bias)
-        self._bias_fused = self.bias is not None
+        bias = None if getattr(self, '_defer_bias', False) else self.bias
+        out = ops.gather_reduce(x, adj, norm, 'sum', bias)
+        self._bias_fused = bias is not None
         return out
 
     def message(self, x_j, norm):
@@ -128,6 +154,8 @@ class GCNConv(MessagePassing):
         if getattr(self, '_bias_fused', False):
             self._bias_fused = False  # the fused kernel's epilogue already added it
             return aggr_out
+        if getattr(self, '_defer_bias', False):
+            return aggr_out  # (A X) W + b: the bias follows the transform in forward()
         if self.bias is not None:
             aggr_out = aggr_out + self.bias
         return aggr_out
@@ -138,6 +166,7 @@ class GCNConv(MessagePassing):
         state['cached_result'] = None
         state['cached_num_edges'] = None
         state.pop('_bias_fused', None)
+        state.pop('_defer_bias', None)
         return state
 
     def __repr__(self):
