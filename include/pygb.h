@@ -251,6 +251,21 @@ int pygb_gat_edge_grad(const float* xw, int64_t ldx, const float* a_src,
                        const float* grad_out, int64_t ldg, const float* row_max,
                        const float* row_sum, float* alpha, float* ds, pygb_stream_t s);
 
+/* ---- K5: dense node-feature transform on the tensor cores ------------------ */
+
+/* C[M,N] = A[M,K] . W[K,N] (+ bias[N]), fp32 in / fp32 out — the
+ * `torch.matmul(x, self.weight)` of GCNConv.forward / GATConv.forward (A.9/A.10;
+ * ref sites examples/gcn.py:25,27, ConvexPruning.py:196,221).  tcgen05.mma
+ * kind::tf32 with TMA-staged operands and the accumulator in TMEM.
+ * passes = 3: 3xTF32 split (Ah.Wh + Al.Wh + Ah.Wl), fp32-faithful (~1e-6 relative);
+ * passes = 1: plain TF32 (10-bit mantissa inputs).  A must be 16-byte aligned with
+ * lda % 4 == 0 (else PYGB_E_UNSUPPORTED: the caller uses its library GEMM).  `ws`
+ * holds the split, transposed copy of W (pygb_gemm_weight_workspace bytes). */
+size_t pygb_gemm_weight_workspace(int64_t K, int64_t N);
+int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
+                 int64_t ldw, int64_t N, const float* bias, float* C, int64_t ldc,
+                 int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,440 @@
+// K5 — the dense node-feature transform  C[M,N] = A[M,K] · W[K,N] (+ bias)  on the
+// 5th-generation tensor cores (tcgen05.mma, accumulator in TMEM, operands staged by
+// TMA into 128-byte-swizzled shared memory).  Replaces `torch.matmul(x, self.weight)`
+// of GCNConv.forward / GATConv.forward (cuBLAS SIMT sgemm in the
+// reference, because its inputs are fp32).
+//
+// fp32 fidelity.  kind::tf32 keeps 10 mantissa bits of each operand, which alone
+// would miss the fp32 parity bar.  The kernel therefore runs the 3xTF32 split
+//     A = Ah + Al,  W = Wh + Wl   (h = round-to-tf32, l = tf32 of the remainder)
+//     C = Ah·Wh + Al·Wh + Ah·Wl   (fp32 accumulation in TMEM)
+// whose error is ~2^-21 relative per product — below fp32 accumulation noise at
+// these K.  Wh/Wl are prepared once per call (tiny); Ah/Al are produced on the fly
+// from the TMA-landed tile by four "splitter" warps, in place, before the MMA warp
+// consumes the stage.  The layer is HBM-bound (M = 2.4M rows, K,N <= 256), so the two
+// extra MMAs hide under the memory time.
+//
+// CTA = 6 warps: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer (one
+// elected lane), warps 2-5 splitter then epilogue (TMEM -> registers -> global).
+// Tile 128 x BN (BN = N rounded to 16, <= 256) x 32 (one 128-byte swizzle atom of
+// fp32), 2-4 stages.  Barriers per stage: full (TMA bytes landed) -> ready (split
+// done, 128 arrivals) -> empty (tcgen05.commit after the MMAs read the stage).
+#include <cuda.h>
+
+#include <mutex>
+
+#include "common.cuh"
+
+namespace pygb {
+namespace {
+
+constexpr int kBM = 128;
+constexpr int kBK = 32;  // fp32 elements = 128 bytes = one swizzle atom
+constexpr int kGemmThreads = 192;
+constexpr int kATileBytes = kBM * kBK * 4;  // 16 KB
+
+// ---- PTX wrappers ---------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tcgen05_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   bar)
+               : "memory");
+}
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                         uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32"
+      " {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+
+// K-major, 128-byte swizzle, rows of 128 bytes packed: 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) |
+         (2ull << 61);
+}
+
+struct GemmParams {
+  const float* bias;
+  float* C;
+  int64_t ldc;
+  int M, N, K;
+  int BN;        // N tile (multiple of 16, <= 256)
+  int stages;    // 2..4
+  int tmem_cols;  // power of two >= max(32, BN)
+};
+
+// PASSES = 3: 3xTF32 split (fp32-faithful);  PASSES = 1: plain TF32.
+template <int PASSES>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBh,
+                 const __grid_constant__ CUtensorMap mapBl, const GemmParams P) {
+  extern __shared__ __align__(1024) unsigned char gsm[];
+  __shared__ __align__(8) uint64_t bars[3 * 4 + 1];
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int BN = P.BN, S = P.stages;
+  const uint32_t b_bytes = (uint32_t)BN * kBK * 4;
+  const uint32_t stage_bytes = (PASSES == 3 ? 2 : 1) * (kATileBytes + b_bytes);
+  // 1024-byte aligned base (swizzle atoms)
+  const uint32_t base = (smem_u32(gsm) + 1023u) & ~1023u;
+  auto a_hi = [&](int s) { return base + (uint32_t)s * stage_bytes; };
+  auto a_lo = [&](int s) { return a_hi(s) + kATileBytes; };
+  auto b_hi = [&](int s) { return a_hi(s) + (PASSES == 3 ? 2 : 1) * kATileBytes; };
+  auto b_lo = [&](int s) { return b_hi(s) + b_bytes; };
+  const uint32_t bar0 = smem_u32(bars);
+  auto full = [&](int s) { return bar0 + 8u * s; };
+  auto ready = [&](int s) { return bar0 + 8u * (4 + s); };
+  auto empty = [&](int s) { return bar0 + 8u * (8 + s); };
+  const uint32_t accum_bar = bar0 + 8u * 12;
+
+  const int m0 = blockIdx.x * kBM;
+  const int n0 = blockIdx.y * BN;
+  const int nk = (P.K + kBK - 1) / kBK;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full(s), 1);
+      mbar_init(ready(s), 128);
+      mbar_init(empty(s), 1);
+    }
+    mbar_init(accum_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // TMEM allocation (whole warp), address lands in shared memory
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(&tmem_base_s)),
+                 "r"((uint32_t)P.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_d = tmem_base_s;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBh) : "memory");
+      if (PASSES == 3) asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBl) : "memory");
+      for (int kt = 0; kt < nk; ++kt) {
+        const int s = kt % S;
+        const uint32_t ph = (uint32_t)(kt / S) & 1u;
+        mbar_wait(empty(s), ph ^ 1u);
+        mbar_expect_tx(full(s), kATileBytes + (PASSES == 3 ? 2 : 1) * b_bytes);
+        tma_load_2d(a_hi(s), &mapA, full(s), kt * kBK, m0);
+        tma_load_2d(b_hi(s), &mapBh, full(s), kt * kBK, n0);
+        if (PASSES == 3) tma_load_2d(b_lo(s), &mapBl, full(s), kt * kBK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                             ((uint32_t)(kBM >> 4) << 24);
+      for (int kt = 0; kt < nk; ++kt) {
+        const int s = kt % S;
+        const uint32_t ph = (uint32_t)(kt / S) & 1u;
+        mbar_wait(PASSES == 3 ? ready(s) : full(s), ph);
+        tcgen05_fence_after();
+        const uint64_t dah = smem_desc_sw128(a_hi(s)), dbh = smem_desc_sw128(b_hi(s));
+        const uint64_t dal = smem_desc_sw128(a_lo(s)), dbl = smem_desc_sw128(b_lo(s));
+#pragma unroll
+        for (int k = 0; k < kBK / 8; ++k) {  // UMMA_K = 8 tf32 = 32 bytes -> +2 in the address field
+          const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
+          mma_tf32(tmem_d, dah + 2u * k, dbh + 2u * k, idesc, acc);
+          if (PASSES == 3) {
+            mma_tf32(tmem_d, dal + 2u * k, dbh + 2u * k, idesc, 1u);
+            mma_tf32(tmem_d, dah + 2u * k, dbl + 2u * k, idesc, 1u);
+          }
+        }
+        tcgen05_commit(empty(s));  // frees the stage once the MMAs have read it
+      }
+      tcgen05_commit(accum_bar);  // accumulator complete
+    }
+  } else {
+    // ===== splitter (PASSES == 3), then epilogue: warps 2..5 =====
+    const int t = threadIdx.x - 64;  // 0..127
+    if (PASSES == 3) {
+      for (int kt = 0; kt < nk; ++kt) {
+        const int s = kt % S;
+        const uint32_t ph = (uint32_t)(kt / S) & 1u;
+        mbar_wait(full(s), ph);
+        const uint32_t ah = a_hi(s), al = a_lo(s);
+#pragma unroll
+        for (int i = 0; i < kATileBytes / 16 / 128; ++i) {
+          const uint32_t off = (uint32_t)(t + i * 128) * 16u;
+          float4 v;
+          asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                       : "r"(ah + off));
+          float4 h, l;
+          h.x = round_tf32(v.x); h.y = round_tf32(v.y); h.z = round_tf32(v.z); h.w = round_tf32(v.w);
+          l.x = round_tf32(v.x - h.x); l.y = round_tf32(v.y - h.y);
+          l.z = round_tf32(v.z - h.z); l.w = round_tf32(v.w - h.w);
+          asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(ah + off), "f"(h.x), "f"(h.y),
+                       "f"(h.z), "f"(h.w)
+                       : "memory");
+          asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(al + off), "f"(l.x), "f"(l.y),
+                       "f"(l.z), "f"(l.w)
+                       : "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // visible to the tensor core
+        mbar_arrive(ready(s));
+      }
+    }
+    // ---- epilogue: thread <-> accumulator row (TMEM lane), 16 columns per load ----
+    mbar_wait(accum_bar, 0);
+    tcgen05_fence_after();
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int row = m0 + q * 32 + lane;
+    const bool row_ok = row < P.M;
+    float* crow = P.C + (int64_t)row * P.ldc;
+    const bool vec_ok = (P.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.C) & 15) == 0);
+    for (int c0 = 0; c0 < BN; c0 += 16) {
+      uint32_t r[16];
+      tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+      tmem_ld_wait();
+      if (row_ok) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) {
+          const int col = n0 + c0 + j;
+          float v[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            v[i] = __uint_as_float(r[j + i]);
+            if (P.bias != nullptr && col + i < P.N) v[i] += __ldg(P.bias + col + i);
+          }
+          if (vec_ok && col + 4 <= P.N) {
+            *reinterpret_cast<float4*>(crow + col) = make_float4(v[0], v[1], v[2], v[3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (col + i < P.N) crow[col + i] = v[i];
+          }
+        }
+      }
+    }
+    tcgen05_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
+                 "r"((uint32_t)P.tmem_cols)
+                 : "memory");
+  }
+}
+
+// W [K,N] (row stride ldw) -> Wh, Wl as [Np][Kp] (K-major, zero padded)
+__global__ void __launch_bounds__(256)
+gemm_prep_weight_kernel(const float* __restrict__ W, int64_t ldw, int K, int N, int Kp, int Np,
+                        float* __restrict__ Wh, float* __restrict__ Wl) {
+  const int64_t total = (int64_t)Np * Kp;
+  for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * 256) {
+    const int n = (int)(t / Kp), k = (int)(t - (int64_t)n * Kp);
+    float v = (n < N && k < K) ? W[(int64_t)k * ldw + n] : 0.f;
+    const float h = round_tf32(v);
+    Wh[t] = h;
+    Wl[t] = round_tf32(v - h);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, []() {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D fp32 row-major [rows, cols] with row stride ld (elements); box = [box_rows, 32 cols]
+int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld,
+             int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return PYGB_E_UNSUPPORTED;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) for [%lld x %lld] ld %lld", (int)r,
+              (long long)rows, (long long)cols, (long long)ld);
+    return PYGB_E_CUDA;
+  }
+  return PYGB_OK;
+}
+
+inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+}  // namespace
+}  // namespace pygb
+
+using namespace pygb;
+
+extern "C" {
+
+size_t pygb_gemm_weight_workspace(int64_t K, int64_t N) {
+  const size_t Kp = (size_t)round_up((int)K, kBK), Np = (size_t)round_up((int)N, 16);
+  return 2 * align_up(Kp * Np * sizeof(float), 1024) + 1024;
+}
+
+int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W, int64_t ldw,
+                 int64_t N, const float* bias, float* C, int64_t ldc, int passes, void* ws,
+                 size_t ws_bytes, pygb_stream_t s) {
+  PYGB_REQUIRE(M >= 0 && K > 0 && N > 0 && M < (1ll << 31) - 256 && K < (1 << 20) && N < (1 << 20),
+               "pygb_gemm_xw: bad sizes");
+  PYGB_REQUIRE(passes == 1 || passes == 3, "pygb_gemm_xw: passes must be 1 (tf32) or 3 (3xtf32)");
+  PYGB_REQUIRE(lda >= K && ldw >= N && ldc >= N, "pygb_gemm_xw: bad leading dimensions");
+  if (M == 0) return PYGB_OK;
+  PYGB_REQUIRE(A && W && C && ws, "pygb_gemm_xw: null pointer");
+  if (!aligned16(A) || (lda % 4) != 0) {
+    set_error("pygb_gemm_xw: A must be 16-byte aligned with a row stride that is a multiple of 4");
+    return PYGB_E_UNSUPPORTED;
+  }
+  if (ws_bytes < pygb_gemm_weight_workspace(K, N)) {
+    set_error("pygb_gemm_xw: workspace too small");
+    return PYGB_E_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(s);
+  const int Kp = round_up((int)K, kBK), Np = round_up((int)N, 16);
+  char* wsb = static_cast<char*>(ws);
+  wsb = reinterpret_cast<char*>(align_up(reinterpret_cast<size_t>(wsb), 1024));
+  float* Wh = reinterpret_cast<float*>(wsb);
+  float* Wl = reinterpret_cast<float*>(wsb + align_up((size_t)Kp * Np * sizeof(float), 1024));
+  {
+    int64_t blocks = ceil_div((int64_t)Kp * Np, 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    gemm_prep_weight_kernel<<<(unsigned)blocks, 256, 0, st>>>(W, ldw, (int)K, (int)N, Kp, Np, Wh,
+                                                             Wl);
+    PYGB_LAUNCH_CHECK();
+  }
+  GemmParams P;
+  P.bias = bias;
+  P.C = C;
+  P.ldc = ldc;
+  P.M = (int)M;
+  P.N = (int)N;
+  P.K = (int)K;
+  P.BN = Np < 256 ? Np : 256;
+  int tc = 32;
+  while (tc < P.BN) tc <<= 1;
+  P.tmem_cols = tc;
+  const size_t b_bytes = (size_t)P.BN * kBK * 4;
+  const size_t stage_bytes = (passes == 3 ? 2 : 1) * (kATileBytes + b_bytes);
+  const size_t budget = 225 * 1024;
+  int stages = (int)((budget - 1024) / stage_bytes);
+  if (stages > 4) stages = 4;
+  const int nk = (int)ceil_div(K, kBK);
+  if (stages > nk) stages = nk < 2 ? 2 : nk;
+  PYGB_REQUIRE(stages >= 2, "pygb_gemm_xw: tile does not fit shared memory");
+  P.stages = stages;
+  const size_t smem = stages * stage_bytes + 1024;
+
+  CUtensorMap mapA, mapBh, mapBl;
+  int rc = make_map(&mapA, A, M, K, lda, kBM);
+  if (rc) return rc;
+  rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN);
+  if (rc) return rc;
+  rc = make_map(&mapBl, Wl, Np, Kp, Kp, P.BN);
+  if (rc) return rc;
+
+  dim3 grid((unsigned)ceil_div(M, kBM), (unsigned)ceil_div(Np, P.BN));
+  if (passes == 3) {
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(225 * 1024)));
+    gemm_tf32_kernel<3><<<grid, kGemmThreads, smem, st>>>(mapA, mapBh, mapBl, P);
+  } else {
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(225 * 1024)));
+    gemm_tf32_kernel<1><<<grid, kGemmThreads, smem, st>>>(mapA, mapBh, mapBl, P);
+  }
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+}  // extern "C"

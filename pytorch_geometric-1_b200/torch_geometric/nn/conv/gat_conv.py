@@ -56,10 +56,10 @@ class GATConv(MessagePassing):
             edge_index = self._with_self_loops(edge_index, x.size(self.node_dim))
 
         if torch.is_tensor(x):
-            x = torch.matmul(x, self.weight)
+            x = ops.linear(x, self.weight)
         else:
-            x = (None if x[0] is None else torch.matmul(x[0], self.weight),
-                 None if x[1] is None else torch.matmul(x[1], self.weight))
+            x = (None if x[0] is None else ops.linear(x[0], self.weight),
+                 None if x[1] is None else ops.linear(x[1], self.weight))
 
         return self.propagate(edge_index, size=size, x=x)
 

@@ -93,15 +93,9 @@ class GCNConv(MessagePassing):
         """"""
         agg_first = self._aggregate_first(x)
         if not agg_first:
-            # X·W with the output row padded to 16 bytes so that the aggregation stays on
-            # its 128-bit load path for widths like 7 or 47 (the padding is sliced away).
-            vec = 16 // x.element_size() if x.is_floating_point() else 1
-            pad = (-self.out_channels) % vec if self.out_channels > 1 else 0
-            if pad and x.dim() == 2:
-                w = torch.nn.functional.pad(self.weight, (0, pad))
-                x = torch.matmul(x, w)[:, :self.out_channels]
-            else:
-                x = torch.matmul(x, self.weight)
+            # X·W on the tensor cores (ops.linear); the output row is padded to 16 bytes so
+            # that the aggregation stays on its 128-bit path for widths like 7 or 47.
+            x = ops.linear(x, self.weight)
 
         if self.cached and self.cached_result is not None:
             if edge_index.size(1) != self.cached_num_edges:
@@ -128,9 +122,7 @@ class GCNConv(MessagePassing):
                 h = self.propagate(edge_index, x=x, norm=norm)
             finally:
                 self._defer_bias = False
-            if self.bias is not None:
-                return torch.addmm(self.bias, h, self.weight)
-            return torch.matmul(h, self.weight)
+            return ops.linear(h, self.weight, self.bias)
         return self.propagate(edge_index, x=x, norm=norm)
 
     def _fused_propagate(self, edge_index, size, i, kwargs):

@@ -4,6 +4,8 @@ These are the pieces ``MessagePassing.propagate``, ``utils.scatter_`` and
 ``utils.softmax`` are assembled from.  Everything here launches kernels of
 ``libpygb.so`` on the tensor's current CUDA stream; there is no CPU path.
 """
+import os
+
 import torch
 
 from . import _native as nat
@@ -419,3 +421,74 @@ def gat_propagate(x_src, x_dst, att, bias, adj, H, C, slope):
     itself (ordinary graphs), another tensor (bipartite) or None (x_i = None)."""
     same = x_dst is x_src
     return _GATFused.apply(x_src, None if same else x_dst, att, bias, adj, H, C, slope, same)
+
+
+# --------------------------------------------------------------------------
+# K5: dense transform X @ W (+ bias) on the tensor cores
+# --------------------------------------------------------------------------
+# '3' = 3xTF32 split (fp32-faithful, default), '1' = plain TF32, '0' = library GEMM.
+GEMM_PASSES = int(os.environ.get('PYGB_GEMM', '3'))
+
+
+def _pad4(n, itemsize):
+    vec = 16 // itemsize
+    return (n + vec - 1) // vec * vec if n > 1 else n
+
+
+def _gemm_eligible(x, w):
+    return (GEMM_PASSES in (1, 3) and x.is_cuda and x.dim() == 2 and w.dim() == 2
+            and x.dtype == torch.float32 and w.dtype == torch.float32 and x.size(0) > 0
+            and x.size(1) > 0 and w.size(1) > 0 and x.stride(1) == 1 and x.stride(0) % 4 == 0
+            and x.stride(0) >= x.size(1) and x.data_ptr() % 16 == 0 and w.stride(1) == 1)
+
+
+def gemm_xw_raw(x, w, bias=None, passes=None):
+    """``x @ w (+ bias)`` by the tcgen05 kernel; the result's rows are padded to 16 bytes
+    (a view ``[:, :N]`` is returned) so that a following aggregation stays vectorised."""
+    dev = nat.require_cuda(x, w, bias)
+    M, K = x.shape
+    N = w.size(1)
+    ldc = _pad4(N, 4)
+    out_full = torch.empty((M, ldc), dtype=torch.float32, device=dev)
+    ws_bytes = nat.workspace('pygb_gemm_weight_workspace', K, N)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    b = _f32(bias)
+    nat.call('pygb_gemm_xw', dev, nat.ptr(x), x.stride(0), M, K, nat.ptr(w), w.stride(0), N,
+             nat.ptr(b), nat.ptr(out_full), ldc, int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
+    return out_full[:, :N] if ldc != N else out_full
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, bias):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = bias is not None
+        return gemm_xw_raw(x, w, bias)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            gx = torch.matmul(g, w.t())
+        if ctx.needs_input_grad[1]:
+            gw = torch.matmul(x.t(), g)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = g.sum(0)
+        return gx, gw, gb
+
+
+def linear(x, w, bias=None):
+    """``x @ w (+ bias)`` (the X·W of GCNConv / GATConv).  fp32 2-D CUDA inputs with
+    16-byte aligned rows go to the tcgen05 kernel; anything else to the library GEMM,
+    with the output row padded the same way."""
+    if _gemm_eligible(x, w):
+        return _Linear.apply(x, w, bias)
+    pad = 0
+    if x.dim() == 2 and x.is_floating_point():
+        pad = _pad4(w.size(1), x.element_size()) - w.size(1)
+    if pad:
+        out = torch.matmul(x, torch.nn.functional.pad(w, (0, pad)))[:, :w.size(1)]
+    else:
+        out = torch.matmul(x, w)
+    return out + bias if bias is not None else out

@@ -1,0 +1,64 @@
+"""GPU: K5 (tcgen05 X·W) against an fp64 CPU matmul, through the C ABI."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(1000, 100, 256), (777, 256, 256), (300, 256, 47), (130, 500, 512), (5000, 604, 64),
+          (129, 32, 16), (1, 8, 3), (128, 36, 300), (4097, 64, 8), (256, 1000, 7)]
+
+
+def _rel(a, b):
+    return (a.double().cpu() - b).abs().max().item() / max(b.abs().max().item(), 1e-30)
+
+
+@pytest.mark.parametrize('M,K,N', SHAPES)
+def test_gemm_3xtf32_matches_fp64(dev, M, K, N):
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(M + K + N)
+    x = torch.randn(M, K, generator=g)
+    w = torch.randn(K, N, generator=g) / K ** 0.5
+    b = torch.randn(N, generator=g)
+    ref = x.double() @ w.double() + b.double()
+    assert ops._gemm_eligible(x.to(dev), w.to(dev))
+    got = ops.gemm_xw_raw(x.to(dev), w.to(dev), b.to(dev), passes=3)
+    assert got.shape == (M, N)
+    # 3xTF32 drops the lo*lo term (2^-22) and the tensor core's fp32 accumulator truncates:
+    # 1e-6 .. 5e-6 of the largest entry for K = 100 .. 600, against ~5e-7 for the library's
+    # fp32 FMA chain.  The bar is north_star's fp32 tolerance, 1e-5 relative.
+    assert _rel(got, ref) <= 1e-5, _rel(got, ref)
+    got_nb = ops.gemm_xw_raw(x.to(dev), w.to(dev), None, passes=3)
+    assert _rel(got_nb, x.double() @ w.double()) <= 1e-5
+
+
+@pytest.mark.parametrize('M,K,N', SHAPES[:5])
+def test_gemm_tf32_single_pass(dev, M, K, N):
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(M, K, generator=g)
+    w = torch.randn(K, N, generator=g) / K ** 0.5
+    got = ops.gemm_xw_raw(x.to(dev), w.to(dev), None, passes=1)
+    assert _rel(got, x.double() @ w.double()) <= 3e-3   # 10-bit mantissa inputs
+
+
+def test_linear_autograd_and_fallbacks(dev):
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(500, 64, generator=g).to(dev).requires_grad_(True)
+    w = torch.randn(64, 47, generator=g).to(dev).requires_grad_(True)
+    b = torch.randn(47, generator=g).to(dev).requires_grad_(True)
+    out = ops.linear(x, w, b)
+    ref = x.detach().double() @ w.detach().double() + b.detach().double()
+    assert _rel(out, ref.cpu()) <= 1e-5
+    out.square().sum().backward()
+    xr, wr, br = (t.detach().clone().requires_grad_(True) for t in (x, w, b))
+    (xr @ wr + br).square().sum().backward()
+    for a, r in ((x.grad, xr.grad), (w.grad, wr.grad), (b.grad, br.grad)):
+        assert _rel(a, r.double().cpu()) <= 1e-4
+    # rows that are not 16-byte multiples (K = 7) and bf16 go to the library GEMM
+    x7 = torch.randn(50, 7, generator=g).to(dev)
+    w7 = torch.randn(7, 5, generator=g).to(dev)
+    assert not ops._gemm_eligible(x7, w7)
+    assert _rel(ops.linear(x7, w7), (x7.double() @ w7.double()).cpu()) <= 1e-5
+    xb = x.detach().bfloat16()
+    assert ops.linear(xb, w.detach().bfloat16()).dtype == torch.bfloat16
