@@ -230,6 +230,20 @@ int pygb_gat_forward(int dtype, const void* xw, int64_t ldx, const float* a_src,
                      const float* bias, void* out, int64_t ldo, float* row_max,
                      float* row_sum, pygb_stream_t s);
 
+/* Streaming form of pygb_gat_forward (K2 v2): one pass with an online softmax per
+ * (row, head) over the flagged index stream / sub-item tables of pygb_seg_tables
+ * and pygb_seg_flag_idx; same outputs (out, row_max, row_sum) up to fp32 rounding.
+ * Needs C % (16/sizeof(T)) == 0 and 16-byte aligned rows, else PYGB_E_UNSUPPORTED
+ * (the caller then uses pygb_gat_forward). */
+size_t pygb_gat_stream_workspace(int64_t n_sub, int H, int C);
+int pygb_gat_forward_stream(int dtype, const void* xw, int64_t ldx, const float* a_src,
+                            const float* a_dst, int H, int C, float negative_slope,
+                            const int32_t* rowptr, const int32_t* idx_flagged,
+                            int64_t n_rows, int64_t E, const int32_t* nz_rows,
+                            const int32_t* sub_info, int32_t Ts, int64_t n_sub,
+                            const float* bias, void* out, int64_t ldo, float* row_max,
+                            float* row_sum, void* ws, size_t ws_bytes, pygb_stream_t s);
+
 /* alpha[e,h] of the fused forward, recomputed from the saved row statistics,
  * written in ORIGINAL edge order (e = perm[p], or p if perm == NULL). */
 int pygb_gat_alpha(const float* a_src, const float* a_dst, int H, float negative_slope,

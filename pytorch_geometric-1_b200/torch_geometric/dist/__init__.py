@@ -1,5 +1,6 @@
 from .partition import PartitionPlan, balanced_bounds
 from .halo import HaloExchange
-from .gcn import DistGraph, dist_gcn_layer
+from .gcn import DistGraph, dist_gcn_layer, dist_gcn_forward
 
-__all__ = ['PartitionPlan', 'balanced_bounds', 'HaloExchange', 'DistGraph', 'dist_gcn_layer']
+__all__ = ['PartitionPlan', 'balanced_bounds', 'HaloExchange', 'DistGraph', 'dist_gcn_layer',
+           'dist_gcn_forward']

@@ -1,6 +1,11 @@
 """Halo exchange for the destination-partitioned graph: an all-gather of the
 source-node feature blocks.  ``torch.distributed`` is the plumbing
-(NCCL over NVLink/NVSwitch on GPUs; gloo in the CPU unit tests)."""
+(NCCL over NVLink/NVSwitch on GPUs; gloo in the CPU unit tests).
+
+The gather buffer is ``[P*block, ld]`` (rank-major, every rank's block padded to
+``plan.block`` rows; ``ld`` = the width padded to 16 bytes so the aggregation
+kernel keeps its 128-bit path).  Producers write their rows straight into
+``slot()``, so the collective runs in place."""
 import torch
 import torch.distributed as dist
 
@@ -10,27 +15,55 @@ class HaloExchange(object):
         self.plan = plan
         self.group = group
         self._buf = {}
+        self.bytes_received_total = 0
+        self.event_log = None  # list -> (start, end, bytes) CUDA events per collective (bench.py)
 
-    def _buffers(self, F, dtype, device):
-        key = (F, dtype, device)
-        if key not in self._buf:
-            full = torch.zeros((self.plan.n_padded, F), dtype=dtype, device=device)
-            self._buf = {key: full}  # keep one shape alive
-        return self._buf[key]
+    def _ld(self, F, itemsize):
+        vec = max(16 // itemsize, 1)
+        return (F + vec - 1) // vec * vec if F > 1 else F
+
+    def _buffer(self, F, dtype, device):
+        key = (F, dtype, str(device))
+        buf = self._buf.get(key)
+        if buf is None:
+            ld = self._ld(F, torch.empty((), dtype=dtype).element_size())
+            buf = torch.zeros((self.plan.n_padded, ld), dtype=dtype, device=device)
+            self._buf[key] = buf
+        return buf
+
+    def slot(self, F, dtype, device):
+        """View ``[n_local, ld]`` of this rank's rows inside the gather buffer."""
+        plan = self.plan
+        full = self._buffer(F, dtype, device)
+        r0 = plan.rank * plan.block
+        return full[r0:r0 + plan.n_local]
+
+    def all_gather_slot(self, F):
+        """All-gather in place after the rank's rows were written through ``slot()``;
+        returns the gathered ``[P*block, F]`` view."""
+        plan = self.plan
+        full = [b for (f, _, _), b in self._buf.items() if f == F][-1]
+        if plan.world_size > 1:
+            mine = full[plan.rank * plan.block:(plan.rank + 1) * plan.block]
+            nbytes = self.bytes_received(full.size(1), full.element_size())
+            if self.event_log is not None and full.is_cuda:
+                e0 = torch.cuda.Event(enable_timing=True)
+                e1 = torch.cuda.Event(enable_timing=True)
+                e0.record()
+                dist.all_gather_into_tensor(full, mine, group=self.group)
+                e1.record()
+                self.event_log.append((e0, e1, nbytes))
+            else:
+                dist.all_gather_into_tensor(full, mine, group=self.group)
+            self.bytes_received_total += nbytes
+        return full[:, :F] if full.size(1) != F else full
 
     def all_gather(self, x_local):
-        """x_local [n_local, F] -> gathered [P*block, F] (rank-major, each block
-        padded to ``plan.block`` rows).  The rank's own block is written in place
-        into the gather buffer, so no extra copy of it is made."""
-        plan = self.plan
+        """x_local [n_local, F] -> gathered [P*block, F]."""
         F = x_local.size(1)
-        full = self._buffers(F, x_local.dtype, x_local.device)
-        mine = full[plan.rank * plan.block:(plan.rank + 1) * plan.block]
-        mine[:plan.n_local].copy_(x_local)
-        if plan.world_size > 1:
-            dist.all_gather_into_tensor(full, mine, group=self.group)
-        return full
+        self.slot(F, x_local.dtype, x_local.device)[:, :F].copy_(x_local)
+        return self.all_gather_slot(F)
 
-    def bytes_received(self, F, itemsize):
+    def bytes_received(self, ld, itemsize):
         p = self.plan
-        return (p.world_size - 1) * p.block * F * itemsize
+        return (p.world_size - 1) * p.block * ld * itemsize

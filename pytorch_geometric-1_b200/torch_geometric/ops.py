@@ -360,7 +360,20 @@ class _GATFused(torch.autograd.Function):
         row_max = torch.empty((n_dst, H), dtype=torch.float32, device=dev)
         row_sum = torch.empty((n_dst, H), dtype=torch.float32, device=dev)
         bias2 = _f32(bias)
-        if n_dst > 0:
+        vec = 16 // xs.element_size()
+        if n_dst > 0 and STREAM and C % vec == 0 and F // vec <= 128 and \
+                xs.data_ptr() % 16 == 0 and _ld(xs) % vec == 0 and adj.E > 0:
+            csr = adj.dst
+            Ts, n_sub, nz_rows, sub_info = csr.items(STREAM_T)
+            idxf = csr.flagged('col')
+            ws_bytes = nat.workspace('pygb_gat_stream_workspace', n_sub, H, C)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            nat.call('pygb_gat_forward_stream', dev, nat.dtype_code(xs), nat.ptr(xs), _ld(xs),
+                     nat.ptr(a_src), nat.ptr(a_dst), H, C, float(slope), nat.ptr(csr.rowptr),
+                     nat.ptr(idxf), n_dst, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub,
+                     nat.ptr(bias2), nat.ptr(out), F, nat.ptr(row_max), nat.ptr(row_sum),
+                     nat.ptr(ws), ws_bytes)
+        elif n_dst > 0:
             nat.call('pygb_gat_forward', dev, nat.dtype_code(xs), nat.ptr(xs), _ld(xs),
                      nat.ptr(a_src), nat.ptr(a_dst), H, C, float(slope), nat.ptr(adj.dst.rowptr),
                      nat.ptr(adj.dst.col), n_dst, nat.ptr(bias2), nat.ptr(out), F,
@@ -442,20 +455,26 @@ def _gemm_eligible(x, w):
             and x.stride(0) >= x.size(1) and x.data_ptr() % 16 == 0 and w.stride(1) == 1)
 
 
-def gemm_xw_raw(x, w, bias=None, passes=None):
+def gemm_xw_raw(x, w, bias=None, passes=None, out=None):
     """``x @ w (+ bias)`` by the tcgen05 kernel; the result's rows are padded to 16 bytes
-    (a view ``[:, :N]`` is returned) so that a following aggregation stays vectorised."""
+    (a view ``[:, :N]`` is returned) so that a following aggregation stays vectorised.
+    ``out``: optional ``[M, >=N]`` fp32 destination with unit inner stride (written in place)."""
     dev = nat.require_cuda(x, w, bias)
     M, K = x.shape
     N = w.size(1)
-    ldc = _pad4(N, 4)
-    out_full = torch.empty((M, ldc), dtype=torch.float32, device=dev)
+    if out is None:
+        ldc = _pad4(N, 4)
+        out_full = torch.empty((M, ldc), dtype=torch.float32, device=dev)
+    else:
+        assert out.dtype == torch.float32 and out.size(0) == M and out.size(1) >= N
+        assert out.stride(1) == 1
+        out_full, ldc = out, (out.stride(0) if M > 1 else max(out.size(1), 1))
     ws_bytes = nat.workspace('pygb_gemm_weight_workspace', K, N)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     b = _f32(bias)
     nat.call('pygb_gemm_xw', dev, nat.ptr(x), x.stride(0), M, K, nat.ptr(w), w.stride(0), N,
              nat.ptr(b), nat.ptr(out_full), ldc, int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
-    return out_full[:, :N] if ldc != N else out_full
+    return out_full[:, :N] if out_full.size(1) != N else out_full
 
 
 class _Linear(torch.autograd.Function):
