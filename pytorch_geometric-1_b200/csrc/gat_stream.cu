@@ -65,13 +65,22 @@ struct GatCfg {
 };
 
 __device__ __forceinline__ float leaky_relu(float x, float slope) { return x > 0.f ? x : x * slope; }
+__device__ __forceinline__ float ex2f(float x) {  // 2^x, flush-to-zero, one MUFU
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
 __device__ __forceinline__ float lds_f32(uint32_t a) {
   float r;
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(a));
   return r;
 }
 
-template <typename T, int LPF, int VPL>
+// The running maximum m is kept in the log2 domain (logit * log2(e)) so that every
+// exponential is a single ex2.approx; row_max is converted back on output.
+template <typename T, int LPF, int VPL, bool EXACT>
 __global__ void __launch_bounds__(kStreamWarps * 32)
 gat_stream_kernel(const GatParams P) {
   using Cf = GatCfg<T, LPF, VPL>;
@@ -89,7 +98,7 @@ gat_stream_kernel(const GatParams P) {
   int head[VPL];
 #pragma unroll
   for (int v = 0; v < VPL; ++v) {
-    act[v] = fl + v * LPF < units;
+    act[v] = EXACT || (fl + v * LPF < units);
     head[v] = act[v] ? ((fl + v * LPF) * KV) / P.C : 0;
   }
   const int W = gridDim.x * kStreamWarps;
@@ -146,7 +155,7 @@ gat_stream_kernel(const GatParams P) {
         const int f0 = (fl + v * LPF) * KV;
         store_partial<KV>(acc[v], pr + f0);
         if (f0 % P.C == 0) {
-          pr[P.Fp + head[v]] = m[v];
+          pr[P.Fp + head[v]] = m[v];  // log2 domain
           pr[P.Fp + H + head[v]] = ssum[v];
         }
       }
@@ -173,7 +182,7 @@ gat_stream_kernel(const GatParams P) {
           for (int i = 0; i < KV; ++i) r[i] = acc[v][i] * inv;
           store_row<T, KV>(r, f0, F, 1.f, 0, P.bias, orow);
           if (f0 % P.C == 0) {
-            if (P.row_max) P.row_max[(int64_t)row_cur * H + head[v]] = m[v];
+            if (P.row_max) P.row_max[(int64_t)row_cur * H + head[v]] = m[v] * kLn2;
             if (P.row_sum) P.row_sum[(int64_t)row_cur * H + head[v]] = ssum[v];
           }
         }
@@ -193,81 +202,106 @@ gat_stream_kernel(const GatParams P) {
       }
     };
 
-    auto issue_stage = [&](int st) {
-      const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * Cf::STAGE_B);
-      const int k0 = st * G;
-      if (st > 0 && (k0 & (LPF - 1)) == 0) {
-        idx_cur = idx_nxt;
-        idx_nxt = (k0 + LPF + fl < n_g) ? __ldg(my_idx + k0 + LPF) : 0;
-      }
-      int craw[G];
-      const int lane0 = grp_lane0 + (k0 & (LPF - 1));
+    const bool all_full = (int64_t)(item * EPW + EPW) * Ts <= (int64_t)E;
+
+    auto run = [&](auto full_tag) {
+      constexpr bool FULL = decltype(full_tag)::value;
+      const int nsteps = FULL ? Ts : __shfl_sync(kFull, n_g, 0);
+      const int nstages = (nsteps + G - 1) / G;
+
+      auto issue_stage = [&](int st) {
+        const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * Cf::STAGE_B);
+        const int k0 = st * G;
+        if (st > 0 && (k0 & (LPF - 1)) == 0) {
+          idx_cur = idx_nxt;
+          idx_nxt = (FULL ? k0 + LPF < Ts : k0 + LPF + fl < n_g) ? __ldg(my_idx + k0 + LPF) : 0;
+        }
+        int craw[G];
+        const char* src[G];
+        const float* as[G];
+        const int lane0 = grp_lane0 + (k0 & (LPF - 1));
 #pragma unroll
-      for (int g = 0; g < G; ++g) craw[g] = __shfl_sync(kFull, idx_cur, lane0 + g);
-#pragma unroll
-      for (int g = 0; g < G; ++g) {
-        if (k0 + g < n_g) {
+        for (int g = 0; g < G; ++g) {
+          craw[g] = __shfl_sync(kFull, idx_cur, lane0 + g);
           const uint32_t c = (uint32_t)(craw[g] & 0x7fffffff);
-          const char* src = xb + (uint64_t)c * ldxb;
-          const float* as = a_src + (uint64_t)c * H;
+          src[g] = xb + (uint64_t)c * ldxb;
+          as[g] = a_src + (uint64_t)c * H;
+        }
 #pragma unroll
-          for (int v = 0; v < VPL; ++v) {
-            if (act[v]) {
-              cp_async16(data0 + so + (uint32_t)(g * Cf::DATA_B + v * 512), src + v * LPF * 16);
-              cp_async_small<4>(asrc0 + so + (uint32_t)(g * Cf::ASRC_B + v * 128), as + head[v]);
+        for (int g = 0; g < G; ++g) {
+          if (FULL || k0 + g < n_g) {
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) {
+              if (act[v]) {
+                cp_async16(data0 + so + (uint32_t)(g * Cf::DATA_B + v * 512), src[g] + v * LPF * 16);
+                cp_async_small<4>(asrc0 + so + (uint32_t)(g * Cf::ASRC_B + v * 128),
+                                  as[g] + head[v]);
+              }
             }
           }
         }
-      }
-      if (lead) sts_words<G>(meta0 + so, craw);
-      cp_async_commit();
-    };
+        if (lead) sts_words<G>(meta0 + so, craw);
+        cp_async_commit();
+      };
 
-    auto consume_stage = [&](int st) {
-      const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * Cf::STAGE_B);
-      const int k0 = st * G;
-      uint32_t flags[G];
-      lds_words<G>(meta0 + so, flags);
+      auto consume_stage = [&](int st) {
+        const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * Cf::STAGE_B);
+        const int k0 = st * G;
+        uint32_t flags[G];
+        lds_words<G>(meta0 + so, flags);
 #pragma unroll
-      for (int g = 0; g < G; ++g) {
-        const int k = k0 + g;
-        if (k < n_g) {
+        for (int g = 0; g < G; ++g) {
+          const int k = k0 + g;
+          const bool valid = FULL || k < n_g;
 #pragma unroll
           for (int v = 0; v < VPL; ++v) {
-            if (act[v]) {
-              const uint4 qv = lds128(data0 + so + (uint32_t)(g * Cf::DATA_B + v * 512));
-              const float as = lds_f32(asrc0 + so + (uint32_t)(g * Cf::ASRC_B + v * 128));
-              const float l = leaky_relu(adst[v] + as, slope);
-              const float mn = fmaxf(m[v], l);
-              const float sc = __expf(m[v] - mn);
-              const float p = __expf(l - mn);
+            float l2 = -FLT_MAX;
+            uint4 qv = make_uint4(0, 0, 0, 0);
+            if (valid && act[v]) {
+              qv = lds128(data0 + so + (uint32_t)(g * Cf::DATA_B + v * 512));
+              const float asv = lds_f32(asrc0 + so + (uint32_t)(g * Cf::ASRC_B + v * 128));
+              l2 = leaky_relu(adst[v] + asv, slope) * kLog2e;
+            }
+            // the maximum rarely moves after the first few edges of a row: rescale only then
+            if (__any_sync(kFull, l2 > m[v])) {
+              const float mn = fmaxf(m[v], l2);
+              const float sc = ex2f(m[v] - mn);
               m[v] = mn;
-              ssum[v] = fmaf(ssum[v], sc, p);
+              ssum[v] *= sc;
+#pragma unroll
+              for (int i = 0; i < KV; ++i) acc[v][i] *= sc;
+            }
+            if (valid && act[v]) {
+              const float p = ex2f(l2 - m[v]);
+              ssum[v] += p;
               float f[KV];
               Elem<T>::unpack(qv, f);
 #pragma unroll
-              for (int i = 0; i < KV; ++i) acc[v][i] = fmaf(p, f[i], acc[v][i] * sc);
+              for (int i = 0; i < KV; ++i) acc[v][i] = fmaf(p, f[i], acc[v][i]);
             }
           }
-          if ((int)flags[g] < 0) flush(k);
+          if (valid && (int)flags[g] < 0) flush(k);
         }
-      }
-    };
+      };
 
 #pragma unroll 1
-    for (int st = 0; st < NSTAGE - 1; ++st) {
-      if (st < nstages) issue_stage(st);
-      else cp_async_commit();
-    }
+      for (int st = 0; st < NSTAGE - 1; ++st) {
+        if (st < nstages) issue_stage(st);
+        else cp_async_commit();
+      }
 #pragma unroll 1
-    for (int st = 0; st < nstages; ++st) {
-      if (st + NSTAGE - 1 < nstages) issue_stage(st + NSTAGE - 1);
-      else cp_async_commit();
-      cp_async_wait<NSTAGE - 1>();
-      __syncwarp();
-      consume_stage(st);
-      __syncwarp();
-    }
+      for (int st = 0; st < nstages; ++st) {
+        if (st + NSTAGE - 1 < nstages) issue_stage(st + NSTAGE - 1);
+        else cp_async_commit();
+        cp_async_wait<NSTAGE - 1>();
+        __syncwarp();
+        consume_stage(st);
+        __syncwarp();
+      }
+    };
+    if (all_full) run(std::true_type{});
+    else run(std::false_type{});
+
     if (kdone < n_g) {  // the row continues in the next sub-item
       write_piece(P.partial + (int64_t)(2 * s + (left_open ? 0 : 1)) * pstride);
       if (lead && !left_open) P.tail_row[s] = row_cur;
@@ -303,7 +337,7 @@ gat_stream_fixup_kernel(const GatParams P) {
       float S = 0.f, A = 0.f;
       for (int cc = c; cc <= c_last; ++cc) {
         const float* pr = P.partial + (int64_t)(cc == c ? 2 * c + 1 : 2 * cc) * pstride;
-        const float sc = __expf(pr[P.Fp + h] - M);
+        const float sc = ex2f(pr[P.Fp + h] - M);
         S = fmaf(pr[P.Fp + H + h], sc, S);
         A = fmaf(pr[f], sc, A);
       }
@@ -311,7 +345,7 @@ gat_stream_fixup_kernel(const GatParams P) {
       if (P.bias) r += __ldg(P.bias + f);
       Elem<T>::store(out + (int64_t)row * P.ldo + f, r);
       if (f % C == 0) {
-        if (P.row_max) P.row_max[(int64_t)row * H + h] = M;
+        if (P.row_max) P.row_max[(int64_t)row * H + h] = M * kLn2;
         if (P.row_sum) P.row_sum[(int64_t)row * H + h] = S;
       }
     }
@@ -334,10 +368,10 @@ gat_stream_fixup_kernel(const GatParams P) {
   }
 }
 
-template <typename T, int LPF, int VPL>
-int launch_gat_one(const GatParams& P, cudaStream_t st) {
+template <typename T, int LPF, int VPL, bool EXACT>
+int launch_gat_k(const GatParams& P, cudaStream_t st) {
   using Cf = GatCfg<T, LPF, VPL>;
-  auto kern = gat_stream_kernel<T, LPF, VPL>;
+  auto kern = gat_stream_kernel<T, LPF, VPL, EXACT>;
   static std::mutex mu;
   static int ctas_cache[64] = {0};
   int dev = 0;
@@ -365,6 +399,12 @@ int launch_gat_one(const GatParams& P, cudaStream_t st) {
   kern<<<(unsigned)grid, kStreamWarps * 32, Cf::CTA_B, st>>>(P);
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
+}
+
+template <typename T, int LPF, int VPL>
+int launch_gat_one(const GatParams& P, cudaStream_t st) {
+  if (P.F / Elem<T>::kVec == LPF * VPL) return launch_gat_k<T, LPF, VPL, true>(P, st);
+  return launch_gat_k<T, LPF, VPL, false>(P, st);
 }
 
 template <typename T>

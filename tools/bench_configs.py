@@ -94,7 +94,7 @@ def cfg3(dev, iters):
     n, H, C = data.x.size(0), 8, 8
     t = timeit(fwd, iters)
     bd = breakdown(fwd)
-    k2 = bd.get('pygb_gat_forward', None)
+    k2 = bd.get('pygb_gat_forward_stream', bd.get('pygb_gat_forward', None))
     k2_bytes = e_prime * (4 + 4 * H + 4 * H * C) + n * H * C * 4 + 2 * n * H * 4 + (n + 1) * 4
     return {'cfg': 3, 'workload': 'GATConv 8x8, Reddit-shaped (%d nodes, %d edges, %d after '
             'remove+add self-loops, 602 feats)' % (n, data.edge_index.size(1), e_prime),
