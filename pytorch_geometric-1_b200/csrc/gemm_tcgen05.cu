@@ -14,11 +14,13 @@
 // consumes the stage.  The layer is HBM-bound (M = 2.4M rows, K,N <= 256), so the two
 // extra MMAs hide under the memory time.
 //
-// CTA = 6 warps: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer (one
-// elected lane), warps 2-5 splitter then epilogue (TMEM -> registers -> global).
-// Tile 128 x BN (BN = N rounded to 16, <= 256) x 32 (one 128-byte swizzle atom of
-// fp32), 2-4 stages.  Barriers per stage: full (TMA bytes landed) -> ready (split
-// done, 128 arrivals) -> empty (tcgen05.commit after the MMAs read the stage).
+// Persistent CTAs (one per SM) of 10 warps: warp 0 TMA producer, warp 1 TMEM
+// allocator + MMA issuer (one elected lane), warps 2-5 splitter, warps 6-9 epilogue
+// (TMEM -> registers -> global).  Tile 128 x BN (BN = N rounded to 16, <= 256) x 32
+// (one 128-byte swizzle atom of fp32), 2-4 stages.  Barriers per stage: full (TMA
+// bytes landed) -> ready (split done, 128 arrivals) -> empty (tcgen05.commit after
+// the MMAs read the stage).  Two accumulator buffers in TMEM (acc_full / acc_empty)
+// let the epilogue of tile t run under the main loop of tile t+1.
 #include <cuda.h>
 
 #include <mutex>
@@ -30,8 +32,11 @@ namespace {
 
 constexpr int kBM = 128;
 constexpr int kBK = 32;  // fp32 elements = 128 bytes = one swizzle atom
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;
 constexpr int kATileBytes = kBM * kBK * 4;  // 16 KB
+constexpr int kEpiRowFloats = 36;           // 32 columns + 4 pad: conflict-free 128-bit transposes
+constexpr int kEpiWarpBytes = 32 * kEpiRowFloats * 4;
+constexpr int kEpiBytes = 4 * kEpiWarpBytes;  // staging for the four epilogue warps
 
 // ---- PTX wrappers ---------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -103,6 +108,18 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
         "=r"(r[14]), "=r"(r[15])
       : "r"(taddr));
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32"
+      " {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]),
+        "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]),
+        "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -123,25 +140,27 @@ struct GemmParams {
   float* C;
   int64_t ldc;
   int M, N, K;
-  int BN;        // N tile (multiple of 16, <= 256)
-  int stages;    // 2..4
-  int tmem_cols;  // power of two >= max(32, BN)
+  int BN;         // N tile (multiple of 16, <= 256)
+  int stages;     // 2..4
+  int tmem_cols;  // power of two >= 2*BN (two accumulator buffers)
+  int m_tiles, n_tiles;
 };
 
 // PASSES = 3: 3xTF32 split (fp32-faithful);  PASSES = 1: plain TF32.
+// Persistent: CTA b works on tiles b, b+grid, ...  (n fastest, so the A tile of a
+// row block is re-read from L2 when N spans several tiles).
 template <int PASSES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBh,
                  const __grid_constant__ CUtensorMap mapBl, const GemmParams P) {
   extern __shared__ __align__(1024) unsigned char gsm[];
-  __shared__ __align__(8) uint64_t bars[3 * 4 + 1];
+  __shared__ __align__(8) uint64_t bars[3 * 4 + 4];
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int BN = P.BN, S = P.stages;
   const uint32_t b_bytes = (uint32_t)BN * kBK * 4;
   const uint32_t stage_bytes = (PASSES == 3 ? 2 : 1) * (kATileBytes + b_bytes);
-  // 1024-byte aligned base (swizzle atoms)
-  const uint32_t base = (smem_u32(gsm) + 1023u) & ~1023u;
+  const uint32_t base = (smem_u32(gsm) + 1023u) & ~1023u;  // swizzle atoms: 1024-byte aligned
   auto a_hi = [&](int s) { return base + (uint32_t)s * stage_bytes; };
   auto a_lo = [&](int s) { return a_hi(s) + kATileBytes; };
   auto b_hi = [&](int s) { return a_hi(s) + (PASSES == 3 ? 2 : 1) * kATileBytes; };
@@ -150,11 +169,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   auto full = [&](int s) { return bar0 + 8u * s; };
   auto ready = [&](int s) { return bar0 + 8u * (4 + s); };
   auto empty = [&](int s) { return bar0 + 8u * (8 + s); };
-  const uint32_t accum_bar = bar0 + 8u * 12;
+  auto acc_full = [&](int b) { return bar0 + 8u * (12 + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (14 + b); };
 
-  const int m0 = blockIdx.x * kBM;
-  const int n0 = blockIdx.y * BN;
   const int nk = (P.K + kBK - 1) / kBK;
+  const int n_tiles_total = P.m_tiles * P.n_tiles;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) {
@@ -162,7 +181,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       mbar_init(ready(s), 128);
       mbar_init(empty(s), 1);
     }
-    mbar_init(accum_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(acc_full(b), 1);
+      mbar_init(acc_empty(b), 128);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // TMEM allocation (whole warp), address lands in shared memory
@@ -183,14 +205,18 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBh) : "memory");
       if (PASSES == 3) asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBl) : "memory");
-      for (int kt = 0; kt < nk; ++kt) {
-        const int s = kt % S;
-        const uint32_t ph = (uint32_t)(kt / S) & 1u;
-        mbar_wait(empty(s), ph ^ 1u);
-        mbar_expect_tx(full(s), kATileBytes + (PASSES == 3 ? 2 : 1) * b_bytes);
-        tma_load_2d(a_hi(s), &mapA, full(s), kt * kBK, m0);
-        tma_load_2d(b_hi(s), &mapBh, full(s), kt * kBK, n0);
-        if (PASSES == 3) tma_load_2d(b_lo(s), &mapBl, full(s), kt * kBK, n0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+        const int m0 = (tile / P.n_tiles) * kBM, n0 = (tile % P.n_tiles) * BN;
+        for (int kt = 0; kt < nk; ++kt, ++it) {
+          const int s = it % S;
+          const uint32_t ph = (uint32_t)(it / S) & 1u;
+          mbar_wait(empty(s), ph ^ 1u);
+          mbar_expect_tx(full(s), kATileBytes + (PASSES == 3 ? 2 : 1) * b_bytes);
+          tma_load_2d(a_hi(s), &mapA, full(s), kt * kBK, m0);
+          tma_load_2d(b_hi(s), &mapBh, full(s), kt * kBK, n0);
+          if (PASSES == 3) tma_load_2d(b_lo(s), &mapBl, full(s), kt * kBK, n0);
+        }
       }
     }
   } else if (warp == 1) {
@@ -198,91 +224,137 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     if (lane == 0) {
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
                              ((uint32_t)(kBM >> 4) << 24);
-      for (int kt = 0; kt < nk; ++kt) {
-        const int s = kt % S;
-        const uint32_t ph = (uint32_t)(kt / S) & 1u;
-        mbar_wait(PASSES == 3 ? ready(s) : full(s), ph);
+      int it = 0, tl = 0;
+      for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++tl) {
+        const int buf = tl & 1;
+        mbar_wait(acc_empty(buf), ((uint32_t)(tl >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
         tcgen05_fence_after();
-        const uint64_t dah = smem_desc_sw128(a_hi(s)), dbh = smem_desc_sw128(b_hi(s));
-        const uint64_t dal = smem_desc_sw128(a_lo(s)), dbl = smem_desc_sw128(b_lo(s));
+        const uint32_t dcol = tmem_d + (uint32_t)(buf * BN);
+        for (int kt = 0; kt < nk; ++kt, ++it) {
+          const int s = it % S;
+          const uint32_t ph = (uint32_t)(it / S) & 1u;
+          mbar_wait(PASSES == 3 ? ready(s) : full(s), ph);
+          tcgen05_fence_after();
+          const uint64_t dah = smem_desc_sw128(a_hi(s)), dbh = smem_desc_sw128(b_hi(s));
+          const uint64_t dal = smem_desc_sw128(a_lo(s)), dbl = smem_desc_sw128(b_lo(s));
 #pragma unroll
-        for (int k = 0; k < kBK / 8; ++k) {  // UMMA_K = 8 tf32 = 32 bytes -> +2 in the address field
-          const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
-          mma_tf32(tmem_d, dah + 2u * k, dbh + 2u * k, idesc, acc);
-          if (PASSES == 3) {
-            mma_tf32(tmem_d, dal + 2u * k, dbh + 2u * k, idesc, 1u);
-            mma_tf32(tmem_d, dah + 2u * k, dbl + 2u * k, idesc, 1u);
+          for (int k = 0; k < kBK / 8; ++k) {  // UMMA_K = 8 tf32 = 32 bytes -> +2 in the address field
+            const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
+            mma_tf32(dcol, dah + 2u * k, dbh + 2u * k, idesc, acc);
+            if (PASSES == 3) {
+              mma_tf32(dcol, dal + 2u * k, dbh + 2u * k, idesc, 1u);
+              mma_tf32(dcol, dah + 2u * k, dbl + 2u * k, idesc, 1u);
+            }
           }
+          tcgen05_commit(empty(s));  // frees the stage once the MMAs have read it
         }
-        tcgen05_commit(empty(s));  // frees the stage once the MMAs have read it
+        tcgen05_commit(acc_full(buf));  // accumulator of this tile complete
       }
-      tcgen05_commit(accum_bar);  // accumulator complete
+    }
+  } else if (warp < 6) {
+    // ===== splitter: warps 2..5 (only for the 3xTF32 split) =====
+    if (PASSES == 3) {
+      const int t = threadIdx.x - 64;  // 0..127
+      int it = 0;
+      for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+        for (int kt = 0; kt < nk; ++kt, ++it) {
+          const int s = it % S;
+          const uint32_t ph = (uint32_t)(it / S) & 1u;
+          mbar_wait(full(s), ph);
+          const uint32_t ah = a_hi(s), al = a_lo(s);
+#pragma unroll
+          for (int i = 0; i < kATileBytes / 16 / 128; ++i) {
+            const uint32_t off = (uint32_t)(t + i * 128) * 16u;
+            float4 v;
+            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                         : "r"(ah + off));
+            float4 h, l;
+            h.x = round_tf32(v.x); h.y = round_tf32(v.y);
+            h.z = round_tf32(v.z); h.w = round_tf32(v.w);
+            l.x = round_tf32(v.x - h.x); l.y = round_tf32(v.y - h.y);
+            l.z = round_tf32(v.z - h.z); l.w = round_tf32(v.w - h.w);
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(ah + off), "f"(h.x),
+                         "f"(h.y), "f"(h.z), "f"(h.w)
+                         : "memory");
+            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(al + off), "f"(l.x),
+                         "f"(l.y), "f"(l.z), "f"(l.w)
+                         : "memory");
+          }
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // visible to the tensor core
+          mbar_arrive(ready(s));
+        }
+      }
     }
   } else {
-    // ===== splitter (PASSES == 3), then epilogue: warps 2..5 =====
-    const int t = threadIdx.x - 64;  // 0..127
-    if (PASSES == 3) {
-      for (int kt = 0; kt < nk; ++kt) {
-        const int s = kt % S;
-        const uint32_t ph = (uint32_t)(kt / S) & 1u;
-        mbar_wait(full(s), ph);
-        const uint32_t ah = a_hi(s), al = a_lo(s);
+    // ===== epilogue: warps 6..9.  TMEM lane = accumulator row: each thread reads 32 columns of
+    // its row, the warp transposes the 32x32 block through shared memory and writes full
+    // 128-byte lines (4 rows per instruction) =====
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const uint32_t epi = base + (uint32_t)S * stage_bytes + (uint32_t)(q * kEpiWarpBytes);
+    const bool vec_ok = (P.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.C) & 15) == 0);
+    const int rr = lane >> 3, jj = lane & 7;
+    int tl = 0;
+    for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++tl) {
+      const int m0 = (tile / P.n_tiles) * kBM, n0 = (tile % P.n_tiles) * BN;
+      const int buf = tl & 1;
+      mbar_wait(acc_full(buf), (uint32_t)(tl >> 1) & 1u);
+      tcgen05_fence_after();
+      const int row0 = m0 + q * 32;
+      const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        if (c0 + 32 <= BN) {
+          tmem_ld32(tbase + (uint32_t)c0, r);
+        } else {  // BN is a multiple of 16: a last half chunk
+          tmem_ld16(tbase + (uint32_t)c0, r);
 #pragma unroll
-        for (int i = 0; i < kATileBytes / 16 / 128; ++i) {
-          const uint32_t off = (uint32_t)(t + i * 128) * 16u;
+          for (int j = 16; j < 32; ++j) r[j] = 0u;
+        }
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(
+                           epi + (uint32_t)((lane * kEpiRowFloats + j) * 4)),
+                       "r"(r[j]), "r"(r[j + 1]), "r"(r[j + 2]), "r"(r[j + 3])
+                       : "memory");
+        __syncwarp();
+        const int col = n0 + c0 + jj * 4;
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (P.bias != nullptr) {
+          if (col < P.N) bv.x = __ldg(P.bias + col);
+          if (col + 1 < P.N) bv.y = __ldg(P.bias + col + 1);
+          if (col + 2 < P.N) bv.z = __ldg(P.bias + col + 2);
+          if (col + 3 < P.N) bv.w = __ldg(P.bias + col + 3);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rl = i * 4 + rr;
           float4 v;
           asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
                        : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                       : "r"(ah + off));
-          float4 h, l;
-          h.x = round_tf32(v.x); h.y = round_tf32(v.y); h.z = round_tf32(v.z); h.w = round_tf32(v.w);
-          l.x = round_tf32(v.x - h.x); l.y = round_tf32(v.y - h.y);
-          l.z = round_tf32(v.z - h.z); l.w = round_tf32(v.w - h.w);
-          asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(ah + off), "f"(h.x), "f"(h.y),
-                       "f"(h.z), "f"(h.w)
-                       : "memory");
-          asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(al + off), "f"(l.x), "f"(l.y),
-                       "f"(l.z), "f"(l.w)
-                       : "memory");
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // visible to the tensor core
-        mbar_arrive(ready(s));
-      }
-    }
-    // ---- epilogue: thread <-> accumulator row (TMEM lane), 16 columns per load ----
-    mbar_wait(accum_bar, 0);
-    tcgen05_fence_after();
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < P.M;
-    float* crow = P.C + (int64_t)row * P.ldc;
-    const bool vec_ok = (P.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.C) & 15) == 0);
-    for (int c0 = 0; c0 < BN; c0 += 16) {
-      uint32_t r[16];
-      tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
-      tmem_ld_wait();
-      if (row_ok) {
-#pragma unroll
-        for (int j = 0; j < 16; j += 4) {
-          const int col = n0 + c0 + j;
-          float v[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            v[i] = __uint_as_float(r[j + i]);
-            if (P.bias != nullptr && col + i < P.N) v[i] += __ldg(P.bias + col + i);
-          }
-          if (vec_ok && col + 4 <= P.N) {
-            *reinterpret_cast<float4*>(crow + col) = make_float4(v[0], v[1], v[2], v[3]);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              if (col + i < P.N) crow[col + i] = v[i];
+                       : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
+          v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+          const int row = row0 + rl;
+          if (row < P.M && col < P.N) {
+            float* dst = P.C + (int64_t)row * P.ldc + col;
+            if (vec_ok && col + 4 <= P.N) {
+              *reinterpret_cast<float4*>(dst) = v;
+            } else {
+              dst[0] = v.x;
+              if (col + 1 < P.N) dst[1] = v.y;
+              if (col + 2 < P.N) dst[2] = v.z;
+              if (col + 3 < P.N) dst[3] = v.w;
+            }
           }
         }
+        __syncwarp();
       }
+      tcgen05_fence_before();
+      mbar_arrive(acc_empty(buf));  // 128 arrivals: the MMA warp may overwrite this buffer
     }
-    tcgen05_fence_before();
   }
+  tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
     tcgen05_fence_after();
@@ -402,18 +474,20 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float*
   P.K = (int)K;
   P.BN = Np < 256 ? Np : 256;
   int tc = 32;
-  while (tc < P.BN) tc <<= 1;
-  P.tmem_cols = tc;
+  while (tc < 2 * P.BN) tc <<= 1;
+  P.tmem_cols = tc;  // two accumulator buffers of BN columns
+  P.m_tiles = (int)ceil_div(M, kBM);
+  P.n_tiles = (int)ceil_div(Np, P.BN);
   const size_t b_bytes = (size_t)P.BN * kBK * 4;
   const size_t stage_bytes = (passes == 3 ? 2 : 1) * (kATileBytes + b_bytes);
-  const size_t budget = 225 * 1024;
-  int stages = (int)((budget - 1024) / stage_bytes);
+  const size_t budget = 226 * 1024;
+  int stages = (int)((budget - 1024 - kEpiBytes) / stage_bytes);
   if (stages > 4) stages = 4;
   const int nk = (int)ceil_div(K, kBK);
   if (stages > nk) stages = nk < 2 ? 2 : nk;
   PYGB_REQUIRE(stages >= 2, "pygb_gemm_xw: tile does not fit shared memory");
   P.stages = stages;
-  const size_t smem = stages * stage_bytes + 1024;
+  const size_t smem = stages * stage_bytes + kEpiBytes + 1024;
 
   CUtensorMap mapA, mapBh, mapBl;
   int rc = make_map(&mapA, A, M, K, lda, kBM);
@@ -423,14 +497,21 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float*
   rc = make_map(&mapBl, Wl, Np, Kp, Kp, P.BN);
   if (rc) return rc;
 
-  dim3 grid((unsigned)ceil_div(M, kBM), (unsigned)ceil_div(Np, P.BN));
+  int sms = 148;
+  {
+    int dev = 0;
+    PYGB_CUDA(cudaGetDevice(&dev));
+    PYGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int64_t tiles = (int64_t)P.m_tiles * P.n_tiles;
+  dim3 grid((unsigned)(tiles < sms ? tiles : sms));
   if (passes == 3) {
     PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)(225 * 1024)));
+                                   (int)(226 * 1024)));
     gemm_tf32_kernel<3><<<grid, kGemmThreads, smem, st>>>(mapA, mapBh, mapBl, P);
   } else {
     PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)(225 * 1024)));
+                                   (int)(226 * 1024)));
     gemm_tf32_kernel<1><<<grid, kGemmThreads, smem, st>>>(mapA, mapBh, mapBl, P);
   }
   PYGB_LAUNCH_CHECK();
