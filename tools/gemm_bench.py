@@ -25,15 +25,22 @@ def timeit(fn, iters=10):
 
 
 def main():
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--only', default='')
+    ap.add_argument('--kinds', default='lib,3xtf32,tf32')
+    args = ap.parse_args()
     from torch_geometric import ops
     dev = torch.device('cuda:0')
     shapes = [('cfg5 L1', 2449029, 100, 256), ('cfg5 L2', 2449029, 256, 256),
               ('cfg5 L3', 2449029, 256, 47), ('cfg3 (K padded to 604)', 232965, 604, 64), ('cfg2 L1', 19717, 500, 512)]
     for name, M, K, N in shapes:
+        if args.only and args.only not in name:
+            continue
         x = torch.randn(M, K, device=dev)
         w = torch.randn(K, N, device=dev) / K ** 0.5
         ref = None
-        for kind in ('lib', '3xtf32', 'tf32'):
+        for kind in args.kinds.split(','):
             if kind == 'lib':
                 fn = lambda: torch.matmul(x, w)
             else:
