@@ -120,7 +120,7 @@ seg_stream_kernel(const StreamParams P) {
 
     auto flush = [&](int k) {  // slot k closes the current row of this lane group
       if (!left_open) {
-        const float inv = 1.f / (float)(k + 1 - kstart);
+        const float inv = (float)(k + 1 - kstart);
         T* orow = static_cast<T*>(P.out) + (int64_t)row_cur * P.ldo;
 #pragma unroll
         for (int v = 0; v < VPL; ++v)
@@ -261,7 +261,7 @@ seg_stream_fixup_kernel(const StreamParams P) {
     if (row < 0) continue;
     const int beg = P.rowptr[row], end = P.rowptr[row + 1];
     const int c_last = (end - 1) / P.Ts;
-    const float inv = 1.f / (float)max(end - beg, 1);
+    const float inv = (float)max(end - beg, 1);
     for (int f0 = lane * KV; f0 < Fp; f0 += 32 * KV) {
       float acc[KV];
       const float* pt = P.partial + (int64_t)(2 * c + 1) * Fp + f0;

@@ -59,14 +59,16 @@ struct StreamCfg {
 
 // Final value of a finished row: mean, bias, conversion, store.
 template <typename T, int KV>
-__device__ __forceinline__ void store_row(float* acc, int f0, int F, float inv_cnt, int mean,
+__device__ __forceinline__ void store_row(float* acc, int f0, int F, float cnt, int mean,
                                           const float* __restrict__ bias, T* orow) {
+  if (mean) {  // scatter_mean divides (torch-scatter 2.0.4: out.div_(count)), so do we
 #pragma unroll
-  for (int i = 0; i < KV; ++i) {
-    float r = acc[i];
-    if (mean) r = r * inv_cnt;
-    if (bias && f0 + i < F) r += __ldg(bias + f0 + i);
-    acc[i] = r;
+    for (int i = 0; i < KV; ++i) acc[i] = __fdiv_rn(acc[i], cnt);
+  }
+  if (bias) {
+#pragma unroll
+    for (int i = 0; i < KV; ++i)
+      if (f0 + i < F) acc[i] += __ldg(bias + f0 + i);
   }
   if (f0 + KV <= F) {
     *reinterpret_cast<uint4*>(orow + f0) = Elem<T>::pack(acc);
