@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define PYGB_ABI_VERSION 2
+#define PYGB_ABI_VERSION 3
 
 enum { PYGB_OK = 0, PYGB_E_ARG = -1, PYGB_E_CUDA = -2, PYGB_E_WORKSPACE = -3,
        PYGB_E_UNSUPPORTED = -4 };
@@ -161,6 +161,22 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
                                   int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
                                   void* ws, size_t ws_bytes, pygb_stream_t s);
 
+/* The same kernel with a routed output (feature-sliced multi-GPU aggregation,
+ * DESIGN.md §4): destination row r is stored at
+ *   (T*)out_tab[r / blk_rows] + (r % blk_rows) * ldo,
+ * where out_tab is a DEVICE array of ceil(n_rows / blk_rows) base pointers, one
+ * per block of destination rows — local memory or peer-GPU memory opened with
+ * pygb_peer_open (plain stores over NVLink; the caller orders them against the
+ * consumer with a stream-ordered collective).  All bases 16-byte aligned. */
+int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, int64_t ldx,
+                                         int64_t F, const int32_t* rowptr,
+                                         const int32_t* idx_flagged, const float* edge_w,
+                                         const float* bias, int64_t n_rows, int64_t E,
+                                         const int32_t* nz_rows, const int32_t* sub_info,
+                                         int32_t Ts, int64_t n_sub, void* const* out_tab,
+                                         int64_t blk_rows, int64_t ldo, void* ws,
+                                         size_t ws_bytes, pygb_stream_t s);
+
 /* Same walk with a per-(edge, head) weight: out[i,h,:] = sum_p
  * head_w[wp(p)*H + h] * x[idx[p],h,:], wp(p) = wperm ? wperm[p] : p — GAT's
  * `x_j * alpha.view(-1,H,1)` + scatter_add (A.10) and its transpose. */
@@ -279,6 +295,31 @@ size_t pygb_gemm_weight_workspace(int64_t K, int64_t N);
 int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
                  int64_t ldw, int64_t N, const float* bias, float* C, int64_t ldc,
                  int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
+
+/* ---- multi-GPU: peer memory and the row -> column redistribution ------------ */
+
+/* One process per GPU.  pygb_peer_alloc returns a zeroed device allocation whose
+ * CUDA IPC handle (PYGB_PEER_HANDLE_BYTES bytes) pygb_peer_export writes; another
+ * process of the same box maps it with pygb_peer_open (peer access over
+ * NVLink/NVSwitch is enabled lazily) and unmaps it with pygb_peer_close.  These
+ * replace nothing in the reference (single-device only); they carry
+ * the exchange step of the partitioned configuration. */
+#define PYGB_PEER_HANDLE_BYTES 64
+int pygb_peer_alloc(size_t bytes, void** ptr);
+int pygb_peer_free(void* ptr);
+int pygb_peer_export(const void* ptr, void* handle, size_t handle_bytes);
+int pygb_peer_open(const void* handle, size_t handle_bytes, void** ptr);
+int pygb_peer_close(void* ptr);
+
+/* Row layout -> column layout: src is this rank's rows [n_rows, n_parts*Fc]
+ * (row stride lds); column block q goes to
+ *   (T*)dst_tab[q] + (dst_row0 + r) * ldd + c,   c < Fc,
+ * dst_tab a DEVICE array of n_parts base pointers (local or peer).  relu != 0
+ * applies max(x, 0) on the way (the activation between two layers).  Fc, lds and
+ * ldd are multiples of 16 bytes. */
+int pygb_cols_scatter(int dtype, const void* src, int64_t lds, int64_t n_rows, int64_t Fc,
+                      int32_t n_parts, void* const* dst_tab, int64_t dst_row0, int64_t ldd,
+                      int relu, pygb_stream_t s);
 
 #ifdef __cplusplus
 }

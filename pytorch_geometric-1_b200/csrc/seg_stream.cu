@@ -60,7 +60,27 @@ struct StreamParams {
   float* partial;  // [2*n_sub][Fp] fp32
   int* tail_row;   // [n_sub], pre-set to -1
   int Fp;
+  // routed output (feature-sliced multi-GPU aggregation): row r is stored at
+  // out_tab[r / blk_rows] + out_off + (r % blk_rows) * ldo — the table holds one
+  // (possibly peer-GPU) base pointer per block of blk_rows destination rows.
+  void* const* out_tab;
+  int blk_rows;
+  unsigned blk_magic;  // floor(2^32 / blk_rows) + 1
+  int64_t out_off;  // bytes
 };
+
+template <typename T>
+__device__ __forceinline__ T* out_row(const StreamParams& P, int64_t row) {
+  if (P.out_tab) {
+    // row / blk_rows without a division: the estimate is q or q + 1 for row < 2^31
+    int q = (int)__umulhi((unsigned)row, P.blk_magic);
+    if (q * P.blk_rows > (int)row) --q;
+    char* base = reinterpret_cast<char*>(
+        __ldg(reinterpret_cast<const unsigned long long*>(P.out_tab) + q));
+    return reinterpret_cast<T*>(base + P.out_off) + (int64_t)((int)row - q * P.blk_rows) * P.ldo;
+  }
+  return static_cast<T*>(P.out) + row * P.ldo;
+}
 
 // WEIGHTED: an edge weight stream exists (16-byte aligned).  EXACT: a feature row
 // is exactly LPF*VPL 16-byte units, so no lane is idle and no unit test is needed.
@@ -121,7 +141,7 @@ seg_stream_kernel(const StreamParams P) {
     auto flush = [&](int k) {  // slot k closes the current row of this lane group
       if (!left_open) {
         const float inv = (float)(k + 1 - kstart);
-        T* orow = static_cast<T*>(P.out) + (int64_t)row_cur * P.ldo;
+        T* orow = out_row<T>(P, row_cur);
 #pragma unroll
         for (int v = 0; v < VPL; ++v)
           if (act[v]) store_row<T, KV>(acc[v], (fl + v * LPF) * KV, F, inv, P.mean, P.bias, orow);
@@ -255,7 +275,6 @@ seg_stream_fixup_kernel(const StreamParams P) {
   const int gw = (blockIdx.x * 256 + threadIdx.x) >> 5;
   const int nw = (gridDim.x * 256) >> 5;
   const int F = P.F, Fp = P.Fp;
-  T* out = static_cast<T*>(P.out);
   for (int c = gw; c < P.n_sub; c += nw) {
     const int row = P.tail_row[c];
     if (row < 0) continue;
@@ -272,7 +291,7 @@ seg_stream_fixup_kernel(const StreamParams P) {
 #pragma unroll
         for (int i = 0; i < KV; ++i) acc[i] += ph[i];
       }
-      store_row<T, KV>(acc, f0, F, inv, P.mean, P.bias, out + (int64_t)row * P.ldo);
+      store_row<T, KV>(acc, f0, F, inv, P.mean, P.bias, out_row<T>(P, row));
     }
   }
   // rows without any slot: sum = 0 (+ bias)
@@ -283,7 +302,7 @@ seg_stream_fixup_kernel(const StreamParams P) {
     while (mask) {
       const int l = __ffs(mask) - 1;
       mask &= mask - 1;
-      T* orow = out + (base + l) * P.ldo;
+      T* orow = out_row<T>(P, base + l);
       for (int f = lane; f < F; f += 32)
         Elem<T>::store(orow + f, P.bias ? __ldg(P.bias + f) : 0.f);
     }
@@ -480,12 +499,12 @@ size_t pygb_seg_stream_workspace(int dtype, int64_t n_sub, int64_t F) {
          align_up((size_t)n_sub * sizeof(int), 256) + 256;
 }
 
-int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t ldx, int64_t F,
-                                  const int32_t* rowptr, const int32_t* idx_flagged,
-                                  const float* edge_w, const float* bias, int64_t n_rows,
-                                  int64_t E, const int32_t* nz_rows, const int32_t* sub_info,
-                                  int32_t Ts, int64_t n_sub, void* out, int64_t ldo, void* ws,
-                                  size_t ws_bytes, pygb_stream_t s) {
+static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, int64_t F,
+                           const int32_t* rowptr, const int32_t* idx_flagged, const float* edge_w,
+                           const float* bias, int64_t n_rows, int64_t E, const int32_t* nz_rows,
+                           const int32_t* sub_info, int32_t Ts, int64_t n_sub, void* out,
+                           void* const* out_tab, int64_t blk_rows, int64_t ldo, void* ws,
+                           size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(reduce == PYGB_SUM || reduce == PYGB_MEAN,
                "pygb_seg_gather_reduce_stream: bad reduce %d", reduce);
   PYGB_REQUIRE(dtype == PYGB_F32 || dtype == PYGB_BF16,
@@ -496,11 +515,13 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
   PYGB_REQUIRE(Ts >= 32 && (Ts & (Ts - 1)) == 0 && n_sub == ceil_div(E, Ts),
                "pygb_seg_gather_reduce_stream: bad plan (Ts must be a power of two >= 32)");
   if (n_rows == 0 || F == 0) return PYGB_OK;
-  PYGB_REQUIRE(rowptr && out && (E == 0 || (x && idx_flagged && nz_rows && sub_info)),
+  PYGB_REQUIRE(rowptr && (out || out_tab) && (E == 0 || (x && idx_flagged && nz_rows && sub_info)),
                "pygb_seg_gather_reduce_stream: null pointer");
+  PYGB_REQUIRE(!out_tab || (blk_rows > 1 && blk_rows < (1ll << 31)),
+               "pygb_seg_gather_reduce_stream_routed: bad blk_rows");
   const int esz = dtype == PYGB_F32 ? 4 : 2;
   const int kv = 16 / esz;
-  PYGB_REQUIRE(aligned16(x) && aligned16(out) && ldx % kv == 0 && ldo % kv == 0 &&
+  PYGB_REQUIRE(aligned16(x) && (!out || aligned16(out)) && ldx % kv == 0 && ldo % kv == 0 &&
                    ldx >= padded_f(dtype, F) && ldo >= padded_f(dtype, F) &&
                    ldx * esz < (1ll << 31) && aligned16(edge_w),
                "pygb_seg_gather_reduce_stream: x/out rows (and edge_w) must be 16-byte aligned, "
@@ -529,7 +550,11 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
     P.n_rows = n_rows;
     P.E = (int)E;
     P.mean = reduce == PYGB_MEAN;
-    P.out = static_cast<char*>(out) + f0 * esz;
+    P.out = out ? static_cast<char*>(out) + f0 * esz : nullptr;
+    P.out_tab = out_tab;
+    P.blk_rows = (int)blk_rows;
+    P.blk_magic = out_tab ? (unsigned)((1ull << 32) / (uint64_t)blk_rows + 1) : 0u;
+    P.out_off = f0 * esz;
     P.ldo = ldo;
     P.sub_info = sub_info;
     P.nz_rows = nz_rows;
@@ -543,6 +568,32 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
     if (rc) return rc;
   }
   return PYGB_OK;
+}
+
+int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t ldx, int64_t F,
+                                  const int32_t* rowptr, const int32_t* idx_flagged,
+                                  const float* edge_w, const float* bias, int64_t n_rows,
+                                  int64_t E, const int32_t* nz_rows, const int32_t* sub_info,
+                                  int32_t Ts, int64_t n_sub, void* out, int64_t ldo, void* ws,
+                                  size_t ws_bytes, pygb_stream_t s) {
+  PYGB_REQUIRE(out || n_rows == 0 || F == 0, "pygb_seg_gather_reduce_stream: null pointer");
+  return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
+                         nz_rows, sub_info, Ts, n_sub, out, nullptr, 0, ldo, ws, ws_bytes, s);
+}
+
+int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, int64_t ldx,
+                                         int64_t F, const int32_t* rowptr,
+                                         const int32_t* idx_flagged, const float* edge_w,
+                                         const float* bias, int64_t n_rows, int64_t E,
+                                         const int32_t* nz_rows, const int32_t* sub_info,
+                                         int32_t Ts, int64_t n_sub, void* const* out_tab,
+                                         int64_t blk_rows, int64_t ldo, void* ws, size_t ws_bytes,
+                                         pygb_stream_t s) {
+  PYGB_REQUIRE(out_tab || n_rows == 0 || F == 0,
+               "pygb_seg_gather_reduce_stream_routed: null pointer table");
+  return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
+                         nz_rows, sub_info, Ts, n_sub, nullptr, out_tab, blk_rows, ldo, ws,
+                         ws_bytes, s);
 }
 
 }  // extern "C"

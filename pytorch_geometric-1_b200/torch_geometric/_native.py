@@ -42,6 +42,14 @@ SIGNATURES = {
     'pygb_seg_stream_workspace': (_Z, [_I, _L, _L]),
     'pygb_seg_gather_reduce_stream': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P, _I,
                                            _L, _P, _L, _P, _Z, _P]),
+    'pygb_seg_gather_reduce_stream_routed': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P,
+                                                  _I, _L, _P, _L, _L, _P, _Z, _P]),
+    'pygb_peer_alloc': (_I, [_Z, _P]),
+    'pygb_peer_free': (_I, [_P]),
+    'pygb_peer_export': (_I, [_P, _P, _Z]),
+    'pygb_peer_open': (_I, [_P, _Z, _P]),
+    'pygb_peer_close': (_I, [_P]),
+    'pygb_cols_scatter': (_I, [_I, _P, _L, _L, _L, _I, _P, _L, _L, _I, _P]),
     'pygb_seg_gather_reduce_heads': (_I, [_I, _P, _L, _I, _I, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
     'pygb_gather_rows': (_I, [_I, _P, _L, _L, _P, _L, _P, _L, _P]),
     'pygb_seg_max': (_I, [_I, _P, _L, _L, _P, _P, _P, _L, _L, _F, _I, _P, _L, _P, _P]),
@@ -91,7 +99,7 @@ def load():
             fn = getattr(lib, name)
             fn.restype = res
             fn.argtypes = args
-        if lib.pygb_abi_version() != 2:
+        if lib.pygb_abi_version() != 3:
             raise NativeError('libpygb.so ABI version mismatch')
         _lib = lib
     return _lib
@@ -146,6 +154,14 @@ def call(name, device, *args):
         else:
             rc = getattr(lib, name)(*args, cur.cuda_stream)
     launches += 1
+    if rc != 0:
+        raise NativeError('{} failed ({}): {}'.format(name, rc, lib.pygb_last_error().decode()))
+
+
+def call_host(name, *args):
+    """Invoke a stream-less entry point (allocation / IPC plumbing); raises on error."""
+    lib = load()
+    rc = getattr(lib, name)(*args)
     if rc != 0:
         raise NativeError('{} failed ({}): {}'.format(name, rc, lib.pygb_last_error().decode()))
 

@@ -109,6 +109,46 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
     return out
 
 
+def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, reduce='sum'):
+    """The streaming fused gather-reduce with a routed output: row ``r`` of the
+    result is stored at ``out_tab[r // blk_rows] + (r % blk_rows) * ldo`` (element
+    units of ``x.dtype``) — ``out_tab`` is an int64 CUDA tensor of base addresses,
+    local or peer-GPU (pygb_seg_gather_reduce_stream_routed; feature-sliced
+    multi-GPU aggregation, dist/sliced.py).  Nothing is returned: the caller owns
+    the destinations and orders the stores against their consumers."""
+    dev = nat.require_cuda(x, w_csr, bias, out_tab)
+    x2 = _rows2d(x)
+    F = x2.size(1)
+    vec = 16 // x2.element_size()
+    if not (F > 1 and F % vec == 0 and x2.data_ptr() % 16 == 0 and _ld(x2) % vec == 0
+            and ldo % vec == 0 and out_tab.dtype == torch.int64 and out_tab.is_contiguous()
+            and out_tab.numel() * blk_rows >= csr.n_rows):
+        raise ValueError('seg_gather_reduce_routed_raw: rows must be 16-byte multiples and the '
+                         'pointer table must cover every destination row')
+    if csr.n_rows == 0 or csr.E == 0:
+        raise ValueError('seg_gather_reduce_routed_raw: empty graph')
+    dt = nat.dtype_code(x2)
+    Ts, n_sub, nz_rows, sub_info = csr.items(STREAM_T)
+    idxf = csr.flagged('col')
+    ws_bytes = nat.workspace('pygb_seg_stream_workspace', dt, n_sub, F)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    nat.call('pygb_seg_gather_reduce_stream_routed', dev,
+             nat.MEAN if reduce == 'mean' else nat.SUM, dt, nat.ptr(x2), _ld(x2), F,
+             nat.ptr(csr.rowptr), nat.ptr(idxf), nat.ptr(_f32(w_csr)), nat.ptr(_f32(bias)),
+             csr.n_rows, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub, nat.ptr(out_tab),
+             int(blk_rows), int(ldo), nat.ptr(ws), ws_bytes)
+
+
+def cols_scatter_raw(src, Fc, n_parts, dst_tab, dst_row0, ldd, relu=False):
+    """Row layout -> column layout (pygb_cols_scatter): column block ``q`` of
+    ``src [n, n_parts*Fc]`` is stored at ``dst_tab[q] + (dst_row0 + r) * ldd``."""
+    dev = nat.require_cuda(src, dst_tab)
+    assert src.dim() == 2 and src.stride(1) == 1 and src.size(1) >= Fc * n_parts
+    assert dst_tab.dtype == torch.int64 and dst_tab.numel() >= n_parts
+    nat.call('pygb_cols_scatter', dev, nat.dtype_code(src), nat.ptr(src), _ld(src), src.size(0),
+             int(Fc), int(n_parts), nat.ptr(dst_tab), int(dst_row0), int(ldd), int(bool(relu)))
+
+
 def gather_rows_raw(x, index):
     dev = nat.require_cuda(x, index)
     x2 = _rows2d(x)

@@ -116,3 +116,95 @@ def test_partition_plan_properties():
         own = plans[0].owner(node)
         for r, p in enumerate(plans):
             assert torch.equal(own == r, (node >= p.lo) & (node < p.hi))
+
+
+# ---- feature-sliced layout (dist/sliced.py) ------------------------------------------
+def _sliced_oracle_aggregate(graph, cols, bias):
+    ei, n = graph.edge_index, graph.plan.num_nodes
+    msg = graph.norm.view(-1, 1) * cols[ei[1 - graph.i]]
+    out = O.scatter_('add', msg, ei[graph.i], 0, n)
+    return out + bias if bias is not None else out
+
+
+def _sliced_transform(x, weight, bias, out):
+    y = x @ weight
+    out[:, :y.size(1)].copy_(y + bias if bias is not None else y)
+    return out
+
+
+def _sliced_worker(rank, world, port, q, x_layout):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from torch_geometric.dist import SlicedGraph, sliced_gcn_forward
+        torch.manual_seed(0)
+        n = 301                                        # not a multiple of the world size
+        ei = random_graph(n, n, 4000, 5)
+        ei[1, :600] = 7
+        x = torch.randn(n, 10)                         # 10 columns: padded to 4 * world
+        dims = [(10, 16), (16, 16), (16, 5), (5, 7)]   # (AX)W, (AX)W, A(XW), (AX)W
+        layers = [(torch.randn(a, b) / a ** 0.5, torch.randn(b)) for a, b in dims]
+        ei2, norm = O.gcn_norm(ei, n, dtype=torch.float32)
+        g = SlicedGraph(ei2, norm, n, rank, world, transport='collective', build_adj=False)
+        pl = g.plan
+        assert pl.n_padded >= n and pl.blk * (world - 1) < n
+        xin = g.slice_cols(x) if x_layout == 'cols' else g.local_rows(x).contiguous()
+        out_local = sliced_gcn_forward(g, xin, layers, relu=True, x_layout=x_layout,
+                                       aggregate=_sliced_oracle_aggregate,
+                                       transform=_sliced_transform)
+        assert out_local.shape == (pl.n_local, 7)
+        parts = [torch.zeros(pl.blk, 7) for _ in range(world)]
+        pad = torch.zeros(pl.blk, 7)
+        pad[:pl.n_local] = out_local
+        dist.all_gather(parts, pad)
+        if rank == 0:
+            got = torch.cat(parts)[:n]
+            h = x
+            for k, (w, b) in enumerate(layers):
+                h = O.scatter_('add', norm.view(-1, 1) * (h @ w)[ei2[0]], ei2[1], 0, n) + b
+                if k + 1 < len(layers):
+                    h = torch.relu(h)
+            err = (got - h).abs().max().item() / h.abs().max().item()
+            q.put(('ok', err, g.transport.bytes_sent_total, g.transport.collectives))
+    except Exception as e:  # pragma: no cover
+        q.put(('error', repr(e), None, None))
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world,x_layout', [(2, 'cols'), (2, 'rows'), (3, 'cols')])
+def test_sliced_gcn_gloo(world, x_layout):
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, x_layout))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    status, err, nbytes, ncoll = q.get(timeout=10)
+    assert status == 'ok', err
+    assert err <= 1e-5, err
+    # layout changes: one per aggregation (cols -> rows) + one per rows -> cols
+    assert ncoll == (7 if x_layout == 'cols' else 8) and nbytes > 0
+
+
+def test_slice_plan_properties():
+    from torch_geometric.dist import SlicePlan
+    for n in (2, 7, 301, 2449029):
+        for world in (1, 2, 3, 4, 8):
+            plans = [SlicePlan(n, world, r) for r in range(world)]
+            assert sum(p.n_local for p in plans) == n
+            assert all(p.lo == min(r * p.blk, n) for r, p in enumerate(plans))
+            for F in (1, 5, 47, 100, 256):
+                Fp, Fc = plans[0].widths(F, 4)
+                assert Fp >= F and Fp == Fc * world and Fc % 4 == 0 and Fp - F < 4 * world
+                cover = [plans[0].col_slice(F, 4, r) for r in range(world)]
+                assert cover[0].start == 0 and cover[-1].stop == Fp
+    # exchange volume: P times less than the all-gather of the row partition
+    p8 = SlicePlan(2449029, 8, 0)
+    assert p8.exchange_bytes(256) * 8 <= 7 * p8.blk * 256 * 4 + 8

@@ -1,6 +1,9 @@
-"""GPU, 2 ranks, NCCL: the destination-partitioned GCN forward (native kernels on
-each rank + halo all-gather over NVLink) against the oracle on the whole graph.
-Skipped when fewer than two GPUs are visible."""
+"""GPU, NCCL: the two multi-GPU layouts of the GCN forward against the oracle on
+the whole graph — the destination partition (native kernels + halo all-gather)
+and the feature-sliced layout (dist/sliced.py) with both transports (all-to-all
+and plain stores into CUDA-IPC peer memory).  Two-rank tests are skipped when
+fewer than two GPUs are visible; the routed kernels and a one-rank PeerTransport
+are also checked on a single GPU."""
 import os
 import socket
 
@@ -83,3 +86,126 @@ def test_dist_gcn_two_gpus_nccl():
     status, err = q.get(timeout=10)
     assert status == 'ok', err
     assert err <= 2e-5, err
+
+
+# ---- feature-sliced layout ---------------------------------------------------------
+def _sliced_worker(rank, world, port, q, transport, x_layout):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for p in (root, os.path.join(root, 'pytorch_geometric-1_b200'), os.path.join(root, 'tests')):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device('cuda', rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+    try:
+        from oracle import ref_cpu as O
+        from util import skewed_graph
+        from torch_geometric.dist import SlicedGraph, sliced_gcn_forward
+        from torch_geometric.nn import GCNConv
+        torch.manual_seed(0)
+        n = 3001
+        ei = skewed_graph(n, 60000, 11)
+        x = torch.randn(n, 100)
+        dims = [(100, 256), (256, 256), (256, 47)]
+        layers = [(torch.randn(a, b) / a ** 0.5, torch.randn(b)) for a, b in dims]
+        ei2, norm = GCNConv.norm(ei.to(dev), n, None, False, torch.float32)
+        g = SlicedGraph(ei2, norm, n, rank, world, transport=transport)
+        pl = g.plan
+        xin = g.slice_cols(x.to(dev)) if x_layout == 'cols' else g.local_rows(x.to(dev)).contiguous()
+        lay = [(w.to(dev), b.to(dev)) for w, b in layers]
+        for _ in range(3):                    # buffer reuse across steps (double-buffered rows)
+            out_local = sliced_gcn_forward(g, xin, lay, x_layout=x_layout)
+        parts = [torch.zeros(pl.blk, 47, device=dev) for _ in range(world)]
+        pad = torch.zeros(pl.blk, 47, device=dev)
+        pad[:pl.n_local] = out_local
+        dist.all_gather(parts, pad)
+        if transport == 'peer':
+            g.transport.close()
+        if rank == 0:
+            got = torch.cat(parts)[:n].cpu()
+            e2, nrm = O.gcn_norm(ei, n, dtype=torch.float32)
+            h = x
+            for k, (w, b) in enumerate(layers):
+                h = O.scatter_('add', nrm.view(-1, 1) * (h @ w)[e2[0]], e2[1], 0, n) + b
+                if k + 1 < len(layers):
+                    h = torch.relu(h)
+            q.put(('ok', (got - h).abs().max().item() / h.abs().max().item()))
+    except Exception as e:  # pragma: no cover
+        q.put(('error', repr(e)))
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+def _run_sliced(world, transport, x_layout):
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, transport, x_layout))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    status, err = q.get(timeout=10)
+    assert status == 'ok', err
+    assert err <= 2e-5, err
+
+
+@pytest.mark.parametrize('transport,x_layout', [('collective', 'cols'), ('peer', 'cols'),
+                                                ('peer', 'rows')])
+def test_sliced_gcn_two_gpus(transport, x_layout):
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs')
+    _run_sliced(2, transport, x_layout)
+
+
+@pytest.mark.parametrize('transport', ['collective', 'peer'])
+def test_sliced_gcn_one_gpu(transport):
+    """world_size 1: the same code path (routed stores into the rank's own arena)."""
+    _run_sliced(1, transport, 'cols')
+
+
+def test_routed_gather_reduce_and_cols_scatter(dev):
+    """The routed K1 and the column scatter on one GPU: the pointer table sends row
+    blocks / column blocks to separate local buffers."""
+    from util import skewed_graph, assert_close
+    from torch_geometric import ops
+    from torch_geometric.graph import Adj
+    n, E, F, blk = 1000, 30000, 24, 300
+    ei = skewed_graph(n, E, 3).to(dev)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(n, F, generator=g).to(dev)
+    w = torch.rand(E, generator=g).to(dev)
+    bias = torch.randn(F, generator=g).to(dev)
+    adj = Adj(ei, 1, (n, n))
+    ref = ops.gather_reduce(x, adj, w, 'sum', bias)
+    nblk = (n + blk - 1) // blk
+    ldo = 40                                            # rows live inside a wider matrix
+    bufs = [torch.full((blk, ldo), -7.0, device=dev) for _ in range(nblk)]
+    tab = torch.tensor([b.data_ptr() + 8 * 4 for b in bufs], dtype=torch.int64).to(dev)
+    old = ops.STREAM_T
+    try:
+        for T in (32, None):
+            ops.STREAM_T = T
+            ops.seg_gather_reduce_routed_raw(x, adj.dst, adj.permuted(w, 'dst'), bias, tab, blk, ldo)
+            got = torch.cat([b[:, 8:8 + F] for b in bufs])[:n]
+            assert_close(got, ref, 1e-6, 'routed rows')
+            assert all(float(b[:, :8].min()) == -7.0 and float(b[:, 8 + F:].max()) == -7.0
+                       for b in bufs), 'stores outside the slice'
+    finally:
+        ops.STREAM_T = old
+    # column scatter: [n, 3*8] -> three [n0 + n, 8] buffers, with and without relu
+    src = torch.randn(n, 28, generator=g).to(dev)
+    for relu in (False, True):
+        outs = [torch.full((n + 5, 12), -7.0, device=dev) for _ in range(3)]
+        tab = torch.tensor([o.data_ptr() for o in outs], dtype=torch.int64).to(dev)
+        ops.cols_scatter_raw(src, 8, 3, tab, 5, 12, relu)
+        for q_, o in enumerate(outs):
+            want = src[:, q_ * 8:(q_ + 1) * 8]
+            assert torch.equal(o[5:, :8], torch.relu(want) if relu else want)
+            assert float(o[:5].max()) == -7.0 and float(o[:, 8:].max()) == -7.0
