@@ -52,6 +52,10 @@ def parse():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--workload', default='products', choices=sorted(WORKLOADS))
     ap.add_argument('--dtype', default='f32', choices=['f32', 'bf16'])
+    ap.add_argument('--dist', default='sliced', choices=['sliced', 'sliced-a2a', 'rows'],
+                    help='N>1 layout: feature-sliced aggregation with peer-memory stores '
+                         '(default) or all-to-all, or the destination-row partition with an '
+                         'all-gather halo')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     return ap.parse_args()
@@ -245,7 +249,7 @@ def run_b200(args):
         edge_index = edge_index  # keep: cached=True checks its edge count every call
         n_rows_local = n
         x_in = x_dev
-    else:
+    elif args.dist == 'rows':
         from torch_geometric.dist import DistGraph, dist_gcn_forward
         ei_full, norm_full = GCNConv.norm(edge_index, n, None, False, torch.float32)
         e_prime = ei_full.size(1)
@@ -259,6 +263,23 @@ def run_b200(args):
         def forward(x):
             with torch.no_grad():
                 h = dist_gcn_forward(graph, x, layers, activation=F.relu)
+                return F.log_softmax(h.float(), dim=1)
+    else:
+        from torch_geometric.dist import SlicedGraph, sliced_gcn_forward
+        ei_full, norm_full = GCNConv.norm(edge_index, n, None, False, torch.float32)
+        e_prime = ei_full.size(1)
+        peer = args.dist == 'sliced' and dtype == torch.float32
+        graph = SlicedGraph(ei_full, norm_full, n, rank, world,
+                            transport='peer' if peer else 'collective')
+        x_in = graph.slice_cols(x_dev)                  # this rank's columns of all rows
+        n_rows_local = n
+        del edge_index, x_dev
+        torch.cuda.empty_cache()
+        layers = [(c.weight.detach(), c.bias.detach()) for c in convs]
+
+        def forward(x):
+            with torch.no_grad():
+                h = sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols')
                 return F.log_softmax(h.float(), dim=1)
 
     def barrier():
@@ -276,8 +297,12 @@ def run_b200(args):
         sampler.start()
         time.sleep(0.3)
     nat.event_log = []
-    if world > 1:
+    sliced = world > 1 and args.dist != 'rows'
+    if world > 1 and not sliced:
         graph.halo.event_log = []
+    if sliced:
+        graph.transport.event_log = []
+        sent0, coll0 = graph.transport.bytes_sent_total, graph.transport.collectives
     l0 = nat.launches
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -292,7 +317,21 @@ def run_b200(args):
     launches = nat.launches - l0
     log, nat.event_log = nat.event_log, None
     halo = None
-    if world > 1:
+    if sliced:
+        tr = graph.transport
+        hl, tr.event_log = tr.event_log, None
+        h_bytes = (tr.bytes_sent_total - sent0) / args.steps
+        halo = {'layout': 'feature-sliced: whole graph on every rank, aggregation over the '
+                          "rank's F/P columns of all rows, transform over the rank's rows",
+                'transport': 'plain stores into CUDA-IPC peer memory from the aggregation kernel '
+                             'and the column-scatter kernel; ranks meet at one-element NCCL '
+                             'all-reduces' if tr.fused else 'NCCL all_to_all_single',
+                'bytes_sent_per_gpu_per_step': h_bytes,
+                'collectives_per_step': (tr.collectives - coll0) / args.steps,
+                'ms_per_step': (sum(a.elapsed_time(b) for a, b, _ in hl) / args.steps
+                                if hl else None),
+                'share_of_step': None}
+    elif world > 1:
         hl, graph.halo.event_log = graph.halo.event_log, None
         h_ms = sum(a.elapsed_time(b) for a, b, _ in hl) / args.steps
         h_bytes = sum(nb for _, _, nb in hl) / args.steps
@@ -308,19 +347,21 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed_ms = float(t.item())
     ms_per_step = elapsed_ms / args.steps
-    if halo is not None:
+    if halo is not None and halo.get('ms_per_step'):
         halo['share_of_step'] = halo['ms_per_step'] / ms_per_step
     value = 3.0 * e_prime / (ms_per_step * 1e-3)
 
     # ---- roofline of the dominant kernel: K1 at F = hidden ---------------------
-    K1_NAMES = ('pygb_seg_gather_reduce', 'pygb_seg_gather_reduce_stream')
+    K1_NAMES = ('pygb_seg_gather_reduce', 'pygb_seg_gather_reduce_stream',
+                'pygb_seg_gather_reduce_stream_routed')
+    k1_width = graph.plan.widths(hid, itemsize)[1] if sliced else hid
     k1 = [(e0.elapsed_time(e1), a) for (name, a, e0, e1) in log
-          if name in K1_NAMES and a[4] == hid]
+          if name in K1_NAMES and a[4] == k1_width]
     k1_ms = sum(t for t, _ in k1) / max(len(k1), 1)
     all_k1_ms = sum(e0.elapsed_time(e1) for (name, a, e0, e1) in log
                     if name in K1_NAMES) / args.steps
-    e_local = e_prime if world == 1 else graph.num_edges_local
-    bytes_k1 = k1_bytes(e_local, n_rows_local, hid, itemsize)
+    e_local = e_prime if (world == 1 or sliced) else graph.num_edges_local
+    bytes_k1 = k1_bytes(e_local, n_rows_local, k1_width, itemsize)
     peak, peak_src = peaks()
     achieved = bytes_k1 / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
     traffic = None
@@ -330,7 +371,7 @@ def run_b200(args):
             traffic = json.load(open(tpath)).get(args.dtype)
         except Exception:
             traffic = None
-    roofline = {'bound': 'hbm', 'kernel': 'seg_stream_kernel + fixup (K1 v2), F=%d %s' % (hid, args.dtype),
+    roofline = {'bound': 'hbm', 'kernel': 'seg_stream_kernel + fixup (K1 v2), F=%d %s' % (k1_width, args.dtype),
                 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
                 'frac_of_nominal_8000': achieved / 8000.0, 'peak_source': peak_src,
                 'algorithmic_bytes_per_launch': bytes_k1, 'avg_launch_ms': k1_ms,
@@ -440,7 +481,8 @@ def run_b200(args):
                 'name': args.workload,
                 'edges_per_step': 3 * e_prime,
                 'parallelism': 'single GPU' if world == 1 else
-                               'dst-range partition x%d + all-gather halo (NCCL)' % world,
+                               ('feature-sliced aggregation x%d (%s)' % (world, args.dist) if sliced
+                                else 'dst-range partition x%d + all-gather halo (NCCL)' % world),
                 'l2': 'inputs larger than L2 (X\' = %.2f GB per layer vs 126 MB L2); no flush' %
                       (n * hid * itemsize / 1e9),
             },
@@ -450,6 +492,8 @@ def run_b200(args):
         }
         print(json.dumps(line))
     if world > 1:
+        if sliced and graph.transport.fused:
+            graph.transport.close()
         dist.destroy_process_group()
 
 

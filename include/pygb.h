@@ -290,11 +290,13 @@ int pygb_gat_edge_grad(const float* xw, int64_t ldx, const float* a_src,
  * passes = 3: 3xTF32 split (Ah.Wh + Al.Wh + Ah.Wl), fp32-faithful (~1e-6 relative);
  * passes = 1: plain TF32 (10-bit mantissa inputs).  A must be 16-byte aligned with
  * lda % 4 == 0 (else PYGB_E_UNSUPPORTED: the caller uses its library GEMM).  `ws`
- * holds the split, transposed copy of W (pygb_gemm_weight_workspace bytes). */
+ * holds the split, transposed copy of W (pygb_gemm_weight_workspace bytes).
+ * relu != 0 applies max(x, 0) after the bias in the epilogue (the activation
+ * between two layers when the caller owns the whole forward, dist/sliced.py). */
 size_t pygb_gemm_weight_workspace(int64_t K, int64_t N);
 int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
-                 int64_t ldw, int64_t N, const float* bias, float* C, int64_t ldc,
-                 int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
+                 int64_t ldw, int64_t N, const float* bias, int relu, float* C,
+                 int64_t ldc, int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
 
 /* ---- multi-GPU: peer memory and the row -> column redistribution ------------ */
 

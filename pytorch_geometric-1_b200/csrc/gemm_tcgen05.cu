@@ -137,6 +137,7 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
 
 struct GemmParams {
   const float* bias;
+  int relu;  // max(x, 0) after the bias (NaN stays NaN, like torch.relu)
   float* C;
   int64_t ldc;
   int M, N, K;
@@ -335,6 +336,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                        : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
                        : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
           v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+          if (P.relu) {
+            v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
+            v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
+          }
           const int row = row0 + rl;
           if (row < P.M && col < P.N) {
             float* dst = P.C + (int64_t)row * P.ldc + col;
@@ -436,8 +441,8 @@ size_t pygb_gemm_weight_workspace(int64_t K, int64_t N) {
 }
 
 int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W, int64_t ldw,
-                 int64_t N, const float* bias, float* C, int64_t ldc, int passes, void* ws,
-                 size_t ws_bytes, pygb_stream_t s) {
+                 int64_t N, const float* bias, int relu, float* C, int64_t ldc, int passes,
+                 void* ws, size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(M >= 0 && K > 0 && N > 0 && M < (1ll << 31) - 256 && K < (1 << 20) && N < (1 << 20),
                "pygb_gemm_xw: bad sizes");
   PYGB_REQUIRE(passes == 1 || passes == 3, "pygb_gemm_xw: passes must be 1 (tf32) or 3 (3xtf32)");
@@ -467,6 +472,7 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float*
   }
   GemmParams P;
   P.bias = bias;
+  P.relu = relu != 0;
   P.C = C;
   P.ldc = ldc;
   P.M = (int)M;

@@ -393,6 +393,10 @@ int launch_stream_one(const StreamParams& P, cudaStream_t st) {
                : launch_stream_k<T, LPF, VPL, false, false>(P, st);
 }
 
+// Lane-group shape for a row of `units` 16-byte vectors: LPF lanes x VPL vectors per
+// lane.  Other shapes with the same capacity (e.g. 16x2 or 8x4 instead of 32x1) were
+// measured within 2 % on the products graph (profiles/r01_k1_shapes.md), so only the
+// widest-lane shape of every capacity is instantiated.
 template <typename T>
 int launch_stream(const StreamParams& P, cudaStream_t st) {
   constexpr int KV = Elem<T>::kVec;

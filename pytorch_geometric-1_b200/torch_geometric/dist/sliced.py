@@ -53,8 +53,10 @@ class SlicePlan(object):
         return self.hi - self.lo
 
     def widths(self, F, itemsize=4):
-        """(Fp, Fc): F padded so that every rank's slice is a 16-byte multiple."""
-        unit = max(16 // itemsize, 1) * self.world_size
+        """(Fp, Fc): F padded so that every rank's slice is a 32-byte multiple — rows
+        that start inside a 32-byte sector slow the gather by 20-25 %
+        (profiles/r01_k1_shapes.md)."""
+        unit = max(32 // itemsize, 1) * self.world_size
         Fp = _ceil_div(max(F, 1), unit) * unit
         return Fp, Fp // self.world_size
 
@@ -359,16 +361,17 @@ def _native_aggregate(graph, cols, bias):
     return ops.gather_reduce(cols, graph.adj, graph.norm, 'sum', bias)
 
 
-def _native_transform(x, weight, bias, out):
+def _native_transform(x, weight, bias, out, relu=False):
     from .. import ops
     n = weight.size(1)
     if x.size(0) == 0:
         return out
     if ops._gemm_eligible(x, weight):
-        ops.gemm_xw_raw(x, weight, bias, out=out)
+        ops.gemm_xw_raw(x, weight, bias, out=out, relu=relu)     # bias and ReLU in the epilogue
     else:
         y = torch.matmul(x, weight)
-        out[:, :n].copy_(y + bias if bias is not None else y)
+        y = y + bias if bias is not None else y
+        out[:, :n].copy_(torch.relu(y) if relu else y)
     return out
 
 
@@ -379,42 +382,38 @@ def sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols', aggregate=_
     (``x_layout='cols'``, see ``SlicedGraph.slice_cols``) or its rows ``[n_local, in]``
     (``'rows'``).  Returns this rank's rows ``[n_local, out]`` of the last layer."""
     p, tr = graph.plan, graph.transport
-    state, kind, pending = x, x_layout, False
+    state, kind = x, x_layout
     esz = x.element_size()
+
+    def padded_weight(k, w, rows):
+        if w.size(0) == rows:
+            return w
+        hit = graph._bufs.get(('w', k))
+        if hit is None or hit[0] is not w or hit[1] != w._version or hit[2].size(0) != rows:
+            hit = (w, w._version, _pad_rows(w.detach(), rows).contiguous())
+            graph._bufs[('w', k)] = hit
+        return hit[2]
+
     for k, (w, b) in enumerate(layers):
         fin, fout = w.shape
         fp_in, _ = p.widths(fin, esz)
         fp_out, _ = p.widths(fout, esz)
+        act = bool(relu) and k + 1 < len(layers)
+        out = graph.buffer(('y', k), p.n_local, fp_out, w.dtype)
         if fin <= fout:                                   # (A X) W: aggregate at width fin
             if kind == 'rows':
-                state = tr.rows_to_cols(state, fin, pending)
-            elif pending:
-                state = torch.relu(state)
+                state = tr.rows_to_cols(state, fin, False)
             rows = tr.aggregate_to_rows(graph, state, fin, None, aggregate)   # [n_local, fp_in]
-            wp = graph._bufs.get(('w', k))
-            if wp is None or wp[0] is not w or wp[1] != w._version:
-                wp = (w, w._version, _pad_rows(w.detach(), fp_in).contiguous())
-                graph._bufs[('w', k)] = wp
-            out = graph.buffer(('y', k), p.n_local, fp_out, w.dtype)
-            state = transform(rows, wp[2], b, out)
+            state = transform(rows, padded_weight(k, w, fp_in), b, out, act)  # bias, ReLU fused
         else:                                             # A (X W): aggregate at width fout
             if kind == 'cols':
                 state = tr.cols_to_rows(state, fin)
-            if pending:
-                state = torch.relu_(state) if not state.requires_grad else torch.relu(state)
-            wp = w
-            if state.size(1) != fin:                      # rows carry their padding columns
-                wp = graph._bufs.get(('w', k))
-                if wp is None or wp[0] is not w or wp[1] != w._version:
-                    wp = (w, w._version, _pad_rows(w.detach(), state.size(1)).contiguous())
-                    graph._bufs[('w', k)] = wp
-                wp = wp[2]
-            out = graph.buffer(('y', k), p.n_local, fp_out, w.dtype)
-            t = transform(state, wp, None, out)
+            t = transform(state, padded_weight(k, w, state.size(1)), None, out, False)
             cols = tr.rows_to_cols(t, fout, False)
-            state = tr.aggregate_to_rows(graph, cols, fout, b, aggregate)
-        kind, pending = 'rows', bool(relu) and k + 1 < len(layers)
+            state = tr.aggregate_to_rows(graph, cols, fout, b, aggregate)     # bias fused
+            if act:
+                state = torch.relu_(state)
+        kind = 'rows'
     if kind == 'cols':                                    # no layers
         return state
-    fout = layers[-1][0].size(1)
-    return state[:, :fout]
+    return state[:, :layers[-1][0].size(1)]

@@ -495,7 +495,7 @@ def _gemm_eligible(x, w):
             and x.stride(0) >= x.size(1) and x.data_ptr() % 16 == 0 and w.stride(1) == 1)
 
 
-def gemm_xw_raw(x, w, bias=None, passes=None, out=None):
+def gemm_xw_raw(x, w, bias=None, passes=None, out=None, relu=False):
     """``x @ w (+ bias)`` by the tcgen05 kernel; the result's rows are padded to 16 bytes
     (a view ``[:, :N]`` is returned) so that a following aggregation stays vectorised.
     ``out``: optional ``[M, >=N]`` fp32 destination with unit inner stride (written in place)."""
@@ -513,7 +513,8 @@ def gemm_xw_raw(x, w, bias=None, passes=None, out=None):
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     b = _f32(bias)
     nat.call('pygb_gemm_xw', dev, nat.ptr(x), x.stride(0), M, K, nat.ptr(w), w.stride(0), N,
-             nat.ptr(b), nat.ptr(out_full), ldc, int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
+             nat.ptr(b), int(bool(relu)), nat.ptr(out_full), ldc, int(passes or GEMM_PASSES),
+             nat.ptr(ws), ws_bytes)
     return out_full[:, :N] if out_full.size(1) != N else out_full
 
 

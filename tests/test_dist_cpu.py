@@ -126,9 +126,10 @@ def _sliced_oracle_aggregate(graph, cols, bias):
     return out + bias if bias is not None else out
 
 
-def _sliced_transform(x, weight, bias, out):
+def _sliced_transform(x, weight, bias, out, relu=False):
     y = x @ weight
-    out[:, :y.size(1)].copy_(y + bias if bias is not None else y)
+    y = y + bias if bias is not None else y
+    out[:, :y.size(1)].copy_(torch.relu(y) if relu else y)
     return out
 
 
@@ -202,7 +203,7 @@ def test_slice_plan_properties():
             assert all(p.lo == min(r * p.blk, n) for r, p in enumerate(plans))
             for F in (1, 5, 47, 100, 256):
                 Fp, Fc = plans[0].widths(F, 4)
-                assert Fp >= F and Fp == Fc * world and Fc % 4 == 0 and Fp - F < 4 * world
+                assert Fp >= F and Fp == Fc * world and Fc % 8 == 0 and Fp - F < 8 * world
                 cover = [plans[0].col_slice(F, 4, r) for r in range(world)]
                 assert cover[0].start == 0 and cover[-1].stop == Fp
     # exchange volume: P times less than the all-gather of the row partition

@@ -31,6 +31,22 @@ def test_gemm_3xtf32_matches_fp64(dev, M, K, N):
     assert _rel(got_nb, x.double() @ w.double()) <= 1e-5
 
 
+@pytest.mark.parametrize('M,K,N', [(1000, 104, 256), (300, 256, 47)])
+def test_gemm_fused_relu_and_padded_output(dev, M, K, N):
+    """relu flag == torch.relu of the unfused result, bit for bit; columns of a wider
+    output matrix beyond N are left untouched."""
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(M, K, generator=g).to(dev)
+    w = (torch.randn(K, N, generator=g) / K ** 0.5).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    plain = ops.gemm_xw_raw(x, w, b)
+    out = torch.full((M, N + 9), -7.0, device=dev)
+    fused = ops.gemm_xw_raw(x, w, b, out=out, relu=True)
+    assert torch.equal(fused, torch.relu(plain))
+    assert float(out[:, N:].max()) == -7.0 and float(out[:, N:].min()) == -7.0
+
+
 @pytest.mark.parametrize('M,K,N', SHAPES[:5])
 def test_gemm_tf32_single_pass(dev, M, K, N):
     from torch_geometric import ops
