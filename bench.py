@@ -56,6 +56,8 @@ def parse():
                     help='N>1 layout: feature-sliced aggregation with peer-memory stores '
                          '(default) or all-to-all, or the destination-row partition with an '
                          'all-gather halo')
+    ap.add_argument('--row-groups', type=int, default=0,
+                    help='sliced layout: number of row groups (0 = 2 on 8 GPUs, else 1)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     return ap.parse_args()
@@ -269,8 +271,10 @@ def run_b200(args):
         ei_full, norm_full = GCNConv.norm(edge_index, n, None, False, torch.float32)
         e_prime = ei_full.size(1)
         peer = args.dist == 'sliced' and dtype == torch.float32
+        row_groups = args.row_groups or (2 if world >= 8 else 1)
         graph = SlicedGraph(ei_full, norm_full, n, rank, world,
-                            transport='peer' if peer else 'collective')
+                            transport='peer' if peer else 'collective', row_groups=row_groups)
+        del ei_full, norm_full
         x_in = graph.slice_cols(x_dev)                  # this rank's columns of all rows
         n_rows_local = n
         del edge_index, x_dev
@@ -308,8 +312,10 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.nvtx.range_push('timed')
     ev0.record()
+    t_host = time.perf_counter()
     for _ in range(args.steps):
         out = forward(x_in)
+    host_ms = (time.perf_counter() - t_host) * 1e3 / args.steps    # CPU time to issue one step
     ev1.record()
     barrier()
     torch.cuda.nvtx.range_pop()
@@ -360,7 +366,9 @@ def run_b200(args):
     k1_ms = sum(t for t, _ in k1) / max(len(k1), 1)
     all_k1_ms = sum(e0.elapsed_time(e1) for (name, a, e0, e1) in log
                     if name in K1_NAMES) / args.steps
-    e_local = e_prime if (world == 1 or sliced) else graph.num_edges_local
+    e_local = e_prime if world == 1 else graph.num_edges_local
+    if sliced:
+        n_rows_local = graph.plan.n_group
     bytes_k1 = k1_bytes(e_local, n_rows_local, k1_width, itemsize)
     peak, peak_src = peaks()
     achieved = bytes_k1 / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
@@ -377,6 +385,19 @@ def run_b200(args):
                 'algorithmic_bytes_per_launch': bytes_k1, 'avg_launch_ms': k1_ms,
                 'k1_share_of_step': all_k1_ms / ms_per_step if ms_per_step > 0 else None,
                 'traffic': traffic}
+
+    # per-entry-point device time inside the timed region (CUDA events around every C-ABI call)
+    breakdown = {}
+    for (name, a, e0, e1) in log:
+        key = name.replace('pygb_', '')
+        if name in K1_NAMES:
+            key += ':F=%d' % a[4]
+        elif name in ('pygb_gemm_xw', 'pygb_gemm_xw_routed'):
+            key += ':K=%d,N=%d' % (a[3], a[6])
+        breakdown[key] = breakdown.get(key, 0.0) + e0.elapsed_time(e1) / args.steps
+    breakdown = {k: round(v, 4) for k, v in breakdown.items()}
+    breakdown['other (framework elementwise ops, fences, waiting on peers)'] = round(
+        ms_per_step - sum(breakdown.values()), 4)
 
     # ---- end to end: host buffers -> public API -> host result ----------------
     e2e = None
@@ -481,13 +502,14 @@ def run_b200(args):
                 'name': args.workload,
                 'edges_per_step': 3 * e_prime,
                 'parallelism': 'single GPU' if world == 1 else
-                               ('feature-sliced aggregation x%d (%s)' % (world, args.dist) if sliced
+                               ('feature-sliced aggregation, %d row group(s) x %d column slices '
+                                '(%s)' % (graph.plan.Gr, graph.plan.Gc, args.dist) if sliced
                                 else 'dst-range partition x%d + all-gather halo (NCCL)' % world),
                 'l2': 'inputs larger than L2 (X\' = %.2f GB per layer vs 126 MB L2); no flush' %
                       (n * hid * itemsize / 1e9),
             },
-            'roofline': roofline, 'halo': halo, 'cpu_baseline': cpu, 'e2e': e2e,
-            'gpu_launches': launches,
+            'roofline': roofline, 'breakdown_ms_per_step': breakdown, 'halo': halo, 'cpu_baseline': cpu, 'e2e': e2e,
+            'gpu_launches': launches, 'host_issue_ms_per_step': host_ms,
             'clocks': clocks,
         }
         print(json.dumps(line))

@@ -298,6 +298,18 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float*
                  int64_t ldw, int64_t N, const float* bias, int relu, float* C,
                  int64_t ldc, int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
 
+/* pygb_gemm_xw with the row layout -> column layout redistribution of the
+ * feature-sliced multi-GPU layout fused into the epilogue: N is
+ * N/Fc column blocks of Fc columns; element (r, q*Fc + c) of the result is stored at
+ *   dst_tab[q * n_dup + d] + (dst_row0 + r) * ldd + c      for every d < n_dup,
+ * dst_tab a DEVICE array of (N/Fc) * n_dup base pointers, local or peer-GPU memory
+ * (pygb_peer_open): the tiles leave over NVLink while the main loop of the next
+ * tile runs.  Fc and ldd multiples of 4, bases 16-byte aligned, n_dup <= 4. */
+int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
+                        int64_t ldw, int64_t N, const float* bias, int relu,
+                        float* const* dst_tab, int64_t Fc, int32_t n_dup, int64_t dst_row0,
+                        int64_t ldd, int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
+
 /* ---- multi-GPU: peer memory and the row -> column redistribution ------------ */
 
 /* One process per GPU.  pygb_peer_alloc returns a zeroed device allocation whose
@@ -315,13 +327,13 @@ int pygb_peer_close(void* ptr);
 
 /* Row layout -> column layout: src is this rank's rows [n_rows, n_parts*Fc]
  * (row stride lds); column block q goes to
- *   (T*)dst_tab[q] + (dst_row0 + r) * ldd + c,   c < Fc,
- * dst_tab a DEVICE array of n_parts base pointers (local or peer).  relu != 0
+ *   (T*)dst_tab[q * n_dup + d] + (dst_row0 + r) * ldd + c,   c < Fc, d < n_dup,
+ * dst_tab a DEVICE array of n_parts * n_dup base pointers (local or peer).  relu != 0
  * applies max(x, 0) on the way (the activation between two layers).  Fc, lds and
  * ldd are multiples of 16 bytes. */
 int pygb_cols_scatter(int dtype, const void* src, int64_t lds, int64_t n_rows, int64_t Fc,
-                      int32_t n_parts, void* const* dst_tab, int64_t dst_row0, int64_t ldd,
-                      int relu, pygb_stream_t s);
+                      int32_t n_parts, int32_t n_dup, void* const* dst_tab, int64_t dst_row0,
+                      int64_t ldd, int relu, pygb_stream_t s);
 
 #ifdef __cplusplus
 }

@@ -135,6 +135,8 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
          (2ull << 61);
 }
 
+constexpr int kMaxDup = 4;  // destinations per column block of the routed epilogue
+
 struct GemmParams {
   const float* bias;
   int relu;  // max(x, 0) after the bias (NaN stays NaN, like torch.relu)
@@ -145,6 +147,12 @@ struct GemmParams {
   int stages;     // 2..4
   int tmem_cols;  // power of two >= 2*BN (two accumulator buffers)
   int m_tiles, n_tiles;
+  // routed output (row layout -> column layout fused into the epilogue): column block
+  // q = col / c_fc of row r goes to c_tab[q * c_dup + d] + (c_row0 + r) * c_ldd + col % c_fc
+  // for every d < c_dup (local or peer-GPU bases).  c_tab == nullptr: plain C.
+  float* const* c_tab;
+  int c_fc, c_dup;
+  int64_t c_row0, c_ldd;
 };
 
 // PASSES = 3: 3xTF32 split (fp32-faithful);  PASSES = 1: plain TF32.
@@ -328,6 +336,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           if (col + 2 < P.N) bv.z = __ldg(P.bias + col + 2);
           if (col + 3 < P.N) bv.w = __ldg(P.bias + col + 3);
         }
+        float* route_base[kMaxDup];
+        if (P.c_tab != nullptr && col < P.N) {
+          const int qb = col / P.c_fc;
+          for (int d = 0; d < P.c_dup; ++d)
+            route_base[d] = P.c_tab[qb * P.c_dup + d] + P.c_row0 * P.c_ldd + (col - qb * P.c_fc);
+        }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           const int rl = i * 4 + rr;
@@ -342,6 +356,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           }
           const int row = row0 + rl;
           if (row < P.M && col < P.N) {
+            if (P.c_tab != nullptr) {   // N and c_fc are multiples of 4 here: whole vectors
+              for (int d = 0; d < P.c_dup; ++d)
+                *reinterpret_cast<float4*>(route_base[d] + (int64_t)row * P.c_ldd) = v;
+              continue;
+            }
             float* dst = P.C + (int64_t)row * P.ldc + col;
             if (vec_ok && col + 4 <= P.N) {
               *reinterpret_cast<float4*>(dst) = v;
@@ -440,15 +459,21 @@ size_t pygb_gemm_weight_workspace(int64_t K, int64_t N) {
   return 2 * align_up(Kp * Np * sizeof(float), 1024) + 1024;
 }
 
-int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W, int64_t ldw,
-                 int64_t N, const float* bias, int relu, float* C, int64_t ldc, int passes,
-                 void* ws, size_t ws_bytes, pygb_stream_t s) {
+struct GemmRoute {
+  float* const* tab;
+  int64_t fc, dup, row0, ldd;
+};
+
+static int gemm_xw_impl(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
+                        int64_t ldw, int64_t N, const float* bias, int relu, float* C,
+                        int64_t ldc, const GemmRoute* route, int passes, void* ws,
+                        size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(M >= 0 && K > 0 && N > 0 && M < (1ll << 31) - 256 && K < (1 << 20) && N < (1 << 20),
                "pygb_gemm_xw: bad sizes");
   PYGB_REQUIRE(passes == 1 || passes == 3, "pygb_gemm_xw: passes must be 1 (tf32) or 3 (3xtf32)");
   PYGB_REQUIRE(lda >= K && ldw >= N && ldc >= N, "pygb_gemm_xw: bad leading dimensions");
   if (M == 0) return PYGB_OK;
-  PYGB_REQUIRE(A && W && C && ws, "pygb_gemm_xw: null pointer");
+  PYGB_REQUIRE(A && W && (C || route) && ws, "pygb_gemm_xw: null pointer");
   if (!aligned16(A) || (lda % 4) != 0) {
     set_error("pygb_gemm_xw: A must be 16-byte aligned with a row stride that is a multiple of 4");
     return PYGB_E_UNSUPPORTED;
@@ -473,6 +498,11 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float*
   GemmParams P;
   P.bias = bias;
   P.relu = relu != 0;
+  P.c_tab = route ? route->tab : nullptr;
+  P.c_fc = route ? (int)route->fc : 1;
+  P.c_dup = route ? (int)route->dup : 0;
+  P.c_row0 = route ? route->row0 : 0;
+  P.c_ldd = route ? route->ldd : 0;
   P.C = C;
   P.ldc = ldc;
   P.M = (int)M;
@@ -522,6 +552,27 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float*
   }
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
+}
+
+int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W, int64_t ldw,
+                 int64_t N, const float* bias, int relu, float* C, int64_t ldc, int passes,
+                 void* ws, size_t ws_bytes, pygb_stream_t s) {
+  PYGB_REQUIRE(C || M == 0, "pygb_gemm_xw: null pointer");
+  return gemm_xw_impl(A, lda, M, K, W, ldw, N, bias, relu, C, ldc, nullptr, passes, ws, ws_bytes,
+                      s);
+}
+
+int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
+                        int64_t ldw, int64_t N, const float* bias, int relu,
+                        float* const* dst_tab, int64_t Fc, int32_t n_dup, int64_t dst_row0,
+                        int64_t ldd, int passes, void* ws, size_t ws_bytes, pygb_stream_t s) {
+  PYGB_REQUIRE(dst_tab && Fc > 0 && Fc % 4 == 0 && N % Fc == 0 && n_dup >= 1 && n_dup <= kMaxDup &&
+                   dst_row0 >= 0 && ldd >= Fc && ldd % 4 == 0,
+               "pygb_gemm_xw_routed: N must be a whole number of column blocks of Fc (multiple "
+               "of 4) columns, 1 <= n_dup <= %d", kMaxDup);
+  GemmRoute r{dst_tab, Fc, n_dup, dst_row0, ldd};
+  return gemm_xw_impl(A, lda, M, K, W, ldw, N, bias, relu, nullptr, N, &r, passes, ws, ws_bytes,
+                      s);
 }
 
 }  // extern "C"

@@ -18,14 +18,15 @@
 namespace pygb {
 namespace {
 
-// src [n_rows, lds] -> for q in 0..P-1: dst_tab[q][(row0 + r) * ldd + c] = act(src[r, q*Fc + c])
+// src [n_rows, lds] -> for q < n_parts, k < n_dup:
+//   dst_tab[q*n_dup + k][(row0 + r) * ldd + c] = act(src[r, q*Fc + c])
 // One thread per 16-byte unit; a group of Fc/KV consecutive threads writes one
 // contiguous Fc-wide row slice of one destination rank.
 template <typename T, bool RELU>
 __global__ void __launch_bounds__(256)
 cols_scatter_kernel(const T* __restrict__ src, int64_t lds, int64_t n_rows, int upr /*units/row*/,
-                    int ups /*units per slice*/, void* const* __restrict__ dst_tab, int64_t row0,
-                    int64_t ldd) {
+                    int ups /*units per slice*/, int n_dup, void* const* __restrict__ dst_tab,
+                    int64_t row0, int64_t ldd) {
   constexpr int KV = Elem<T>::kVec;
   const int64_t total = n_rows * upr;
   for (int64_t u = (int64_t)blockIdx.x * 256 + threadIdx.x; u < total;
@@ -41,10 +42,12 @@ cols_scatter_kernel(const T* __restrict__ src, int64_t lds, int64_t n_rows, int 
       for (int i = 0; i < KV; ++i) f[i] = f[i] < 0.f ? 0.f : f[i];  // NaN stays NaN (torch.relu)
       v = Elem<T>::pack(f);
     }
-    T* d = reinterpret_cast<T*>(
-               __ldg(reinterpret_cast<const unsigned long long*>(dst_tab) + q)) +
-           (row0 + r) * ldd + (int64_t)c * KV;
-    *reinterpret_cast<uint4*>(d) = v;
+    for (int k = 0; k < n_dup; ++k) {
+      T* d = reinterpret_cast<T*>(
+                 __ldg(reinterpret_cast<const unsigned long long*>(dst_tab) + q * n_dup + k)) +
+             (row0 + r) * ldd + (int64_t)c * KV;
+      *reinterpret_cast<uint4*>(d) = v;
+    }
   }
 }
 
@@ -91,11 +94,11 @@ int pygb_peer_close(void* ptr) {
 }
 
 int pygb_cols_scatter(int dtype, const void* src, int64_t lds, int64_t n_rows, int64_t Fc,
-                      int32_t n_parts, void* const* dst_tab, int64_t dst_row0, int64_t ldd,
-                      int relu, pygb_stream_t s) {
+                      int32_t n_parts, int32_t n_dup, void* const* dst_tab, int64_t dst_row0,
+                      int64_t ldd, int relu, pygb_stream_t s) {
   PYGB_REQUIRE(dtype == PYGB_F32 || dtype == PYGB_BF16, "pygb_cols_scatter: bad dtype %d", dtype);
   const int esz = dtype == PYGB_F32 ? 4 : 2, kv = 16 / esz;
-  PYGB_REQUIRE(n_rows >= 0 && Fc > 0 && n_parts > 0 && dst_row0 >= 0 && Fc % kv == 0 &&
+  PYGB_REQUIRE(n_rows >= 0 && Fc > 0 && n_parts > 0 && n_dup > 0 && dst_row0 >= 0 && Fc % kv == 0 &&
                    lds % kv == 0 && ldd % kv == 0 && lds >= Fc * n_parts && ldd >= Fc &&
                    Fc * n_parts < (1ll << 24),
                "pygb_cols_scatter: widths must be multiples of 16 bytes (Fc=%lld, lds=%lld, "
@@ -109,11 +112,11 @@ int pygb_cols_scatter(int dtype, const void* src, int64_t lds, int64_t n_rows, i
   do {                                                                                         \
     if (relu)                                                                                  \
       cols_scatter_kernel<TT, true><<<grid, 256, 0, st>>>(static_cast<const TT*>(src), lds,    \
-                                                          n_rows, upr, ups, dst_tab, dst_row0, \
-                                                          ldd);                                \
+                                                          n_rows, upr, ups, n_dup, dst_tab,    \
+                                                          dst_row0, ldd);                      \
     else                                                                                       \
       cols_scatter_kernel<TT, false><<<grid, 256, 0, st>>>(static_cast<const TT*>(src), lds,   \
-                                                           n_rows, upr, ups, dst_tab,          \
+                                                           n_rows, upr, ups, n_dup, dst_tab,   \
                                                            dst_row0, ldd);                     \
   } while (0)
   if (dtype == PYGB_F32) PYGB_SCATTER(float);

@@ -49,7 +49,9 @@ SIGNATURES = {
     'pygb_peer_export': (_I, [_P, _P, _Z]),
     'pygb_peer_open': (_I, [_P, _Z, _P]),
     'pygb_peer_close': (_I, [_P]),
-    'pygb_cols_scatter': (_I, [_I, _P, _L, _L, _L, _I, _P, _L, _L, _I, _P]),
+    'pygb_cols_scatter': (_I, [_I, _P, _L, _L, _L, _I, _I, _P, _L, _L, _I, _P]),
+    'pygb_gemm_xw_routed': (_I, [_P, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _L, _L, _I, _P,
+                                 _Z, _P]),
     'pygb_seg_gather_reduce_heads': (_I, [_I, _P, _L, _I, _I, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
     'pygb_gather_rows': (_I, [_I, _P, _L, _L, _P, _L, _P, _L, _P]),
     'pygb_seg_max': (_I, [_I, _P, _L, _L, _P, _P, _P, _L, _L, _F, _I, _P, _L, _P, _P]),

@@ -25,6 +25,12 @@ transports implement it:
   CUDA-IPC mapped memory; ranks meet at a one-element stream-ordered all-reduce
   after each such kernel (no flags, no spinning).
 
+With ``row_groups = G > 1`` the layout is two-dimensional: the P ranks form G row
+groups of P/G ranks; a rank aggregates only the destination rows of its row group,
+at width ``F / (P/G)``.  Wider slices keep the gather kernel near the HBM roofline
+(its cost per edge has a fixed part: index, weight, issue slots), at the price of
+sending every column block to G ranks.  On 8 GPUs 2 x 4 beats 1 x 8.
+
 The reference has no counterpart (single device).  Aggregation and
 transform are injectable so the host logic runs on CPU under gloo.
 """
@@ -39,34 +45,50 @@ def _ceil_div(a, b):
 
 
 class SlicePlan(object):
-    """Row blocks and column slices of one rank."""
+    """Row blocks, row groups and column slices of one rank.
 
-    def __init__(self, num_nodes, world_size, rank):
+    rank = rg * Gc + cg: row group ``rg`` (of ``Gr``), column slice ``cg`` (of ``Gc``).
+    Row block ``q`` (``blk`` rows) is owned by rank ``q``; row group ``rg`` is the union
+    of the blocks of its ranks."""
+
+    def __init__(self, num_nodes, world_size, rank, row_groups=1):
         self.num_nodes, self.world_size, self.rank = int(num_nodes), int(world_size), int(rank)
+        self.Gr = int(row_groups)
+        if self.Gr < 1 or self.world_size % self.Gr:
+            raise ValueError('row_groups must divide the world size')
+        self.Gc = self.world_size // self.Gr
+        self.rg, self.cg = divmod(self.rank, self.Gc)
         self.blk = max(_ceil_div(self.num_nodes, self.world_size), 2)
         self.n_padded = self.blk * self.world_size
         self.lo = min(self.rank * self.blk, self.num_nodes)
         self.hi = min(self.lo + self.blk, self.num_nodes)
+        self.g_lo = min(self.rg * self.Gc * self.blk, self.num_nodes)
+        self.g_hi = min(self.g_lo + self.Gc * self.blk, self.num_nodes)
 
     @property
     def n_local(self):
         return self.hi - self.lo
 
+    @property
+    def n_group(self):
+        return self.g_hi - self.g_lo
+
     def widths(self, F, itemsize=4):
-        """(Fp, Fc): F padded so that every rank's slice is a 32-byte multiple — rows
+        """(Fp, Fc): F padded so that every column slice is a 32-byte multiple — rows
         that start inside a 32-byte sector slow the gather by 20-25 %
         (profiles/r01_k1_shapes.md)."""
-        unit = max(32 // itemsize, 1) * self.world_size
+        unit = max(32 // itemsize, 1) * self.Gc
         Fp = _ceil_div(max(F, 1), unit) * unit
-        return Fp, Fp // self.world_size
+        return Fp, Fp // self.Gc
 
-    def col_slice(self, F, itemsize=4, rank=None):
+    def col_slice(self, F, itemsize=4, cg=None):
         Fp, Fc = self.widths(F, itemsize)
-        r = self.rank if rank is None else rank
-        return slice(r * Fc, (r + 1) * Fc)
+        c = self.cg if cg is None else cg
+        return slice(c * Fc, (c + 1) * Fc)
 
     def exchange_bytes(self, F, itemsize=4):
-        """Bytes one rank sends in one layout change of an [N, F] matrix."""
+        """Bytes one rank sends when an [N, F] matrix goes from the row layout to the
+        column layout (every column block to the Gr ranks that aggregate it)."""
         Fp, Fc = self.widths(F, itemsize)
         return (self.world_size - 1) * self.blk * Fc * itemsize
 
@@ -85,6 +107,13 @@ def _pad_rows(t, rows):
     out = t.new_zeros((rows,) + tuple(t.shape[1:]))
     out[:t.size(0)] = t
     return out
+
+
+def _bias_slice(plan, bias, F, itemsize):
+    if bias is None:
+        return None
+    Fp, _ = plan.widths(F, itemsize)
+    return _pad_cols(bias.view(1, -1), Fp).view(-1)[plan.col_slice(F, itemsize)].contiguous()
 
 
 class CollectiveTransport(object):
@@ -118,14 +147,21 @@ class CollectiveTransport(object):
         self.collectives += 1
         return recv
 
-    def cols_to_rows(self, cols, F):
-        """cols [>=N, Fc] (this rank's columns of all rows) -> rows [n_local, Fp]."""
+    def group_cols_to_rows(self, z, F):
+        """z [n_group, Fc]: this rank's column slice of the rows of its row group ->
+        rows [n_local, Fp].  Only the ranks of the same row group exchange data."""
         p = self.plan
-        Fp, Fc = p.widths(F, cols.element_size())
-        send = _pad_rows(cols[:, :Fc], p.n_padded).contiguous().view(p.world_size, p.blk, Fc)
-        recv = self._a2a(send)                               # [q] = my rows, columns of rank q
-        rows = recv.permute(1, 0, 2).reshape(p.blk, Fp)
-        return rows[:p.n_local]
+        Fp, Fc = p.widths(F, z.element_size())
+        send = z.new_zeros((p.world_size, p.blk, Fc))
+        mine = _pad_rows(z[:, :Fc], p.Gc * p.blk).view(p.Gc, p.blk, Fc)
+        send[p.rg * p.Gc:(p.rg + 1) * p.Gc] = mine
+        recv = self._a2a(send)[p.rg * p.Gc:(p.rg + 1) * p.Gc]    # [cg'] = my rows, slice cg'
+        return recv.permute(1, 0, 2).reshape(p.blk, Fp)[:p.n_local]
+
+    def cols_to_rows(self, cols, F):
+        """cols [>=N, Fc] (all rows) -> rows [n_local, Fp]: pure redistribution."""
+        p = self.plan
+        return self.group_cols_to_rows(cols[p.g_lo:p.g_hi], F)
 
     def rows_to_cols(self, rows, F, relu=False):
         """rows [n_local, >=F] -> cols [n_padded, Fc] (rows beyond N are padding)."""
@@ -134,17 +170,16 @@ class CollectiveTransport(object):
         r = _pad_rows(_pad_cols(rows[:, :min(rows.size(1), Fp)], Fp), p.blk)
         if relu:
             r = torch.relu(r)
-        send = r.view(p.blk, p.world_size, Fc).permute(1, 0, 2).contiguous()
+        blocks = r.view(p.blk, p.Gc, Fc).permute(1, 0, 2)          # [cg', blk, Fc]
+        send = blocks.repeat(p.Gr, 1, 1).contiguous()              # rank (rg', cg') gets block cg'
         return self._a2a(send).view(p.n_padded, Fc)
 
     def aggregate_to_rows(self, graph, cols, F, bias, aggregate):
-        p = self.plan
-        Fp, Fc = p.widths(F, cols.element_size())
-        b = None
-        if bias is not None:
-            b = _pad_cols(bias.view(1, -1), Fp).view(-1)[p.col_slice(F, cols.element_size())]
-        z = aggregate(graph, cols, b)                        # [N, Fc]
-        return self.cols_to_rows(z, F)
+        b = _bias_slice(self.plan, bias, F, cols.element_size())
+        return self.group_cols_to_rows(aggregate(graph, cols, b), F)       # z: [n_group, Fc]
+
+    def transform_to_cols(self, graph, rows, w, bias, F, relu, transform, out):
+        return self.rows_to_cols(transform(rows, w, bias, out, relu), F, False)
 
 
 class _DevMem(object):
@@ -164,8 +199,11 @@ class PeerTransport(object):
         from .. import _native as nat
         self.nat = nat
         self.plan, self.group, self.device = plan, group, torch.device(device)
+        if plan.Gr > 4:
+            raise ValueError('PeerTransport supports at most 4 row groups')
         self.bytes_sent_total = 0
         self.collectives = 0            # fences (one-element all-reduces), not data
+        self.event_log = None
         self._cap = None                # (Fp_max elements) the arena was sized for
         self._base = None               # this rank's arena
         self._peer = []                 # arena base address of every rank, as seen from here
@@ -179,7 +217,7 @@ class PeerTransport(object):
     def _layout(self, fp_max):
         p = self.plan
         r_bytes = (p.blk * fp_max * 4 + 255) // 256 * 256
-        c_bytes = (p.n_padded * (fp_max // p.world_size) * 4 + 255) // 256 * 256
+        c_bytes = (p.n_padded * (fp_max // p.Gc) * 4 + 255) // 256 * 256
         return r_bytes, c_bytes
 
     def ensure(self, fp_max):
@@ -250,29 +288,56 @@ class PeerTransport(object):
             dist.all_reduce(self._flag, group=self.group)
         self.collectives += 1
 
-    # ---- layout changes ---------------------------------------------------------------
     def _check(self, t):
         if t.dtype != torch.float32 or not t.is_cuda:
             raise TypeError('PeerTransport moves fp32 CUDA tensors')
 
+    def _cols_table(self):
+        """Column block j of this rank's rows goes to the ranks (rg', j) of every row group."""
+        p = self.plan
+        return self._table(('c',), [self._peer[r * p.Gc + j] + self._c_off
+                                    for j in range(p.Gc) for r in range(p.Gr)])
+
+    def _sent_cols(self, Fc):
+        p = self.plan
+        self.bytes_sent_total += (p.world_size - 1) * p.n_local * Fc * 4
+
+    # ---- layout changes ---------------------------------------------------------------
     def aggregate_to_rows(self, graph, cols, F, bias, aggregate=None):
+        """The aggregation kernel stores every finished row slice into the row buffer of
+        the rank that owns the row (peers of the same row group)."""
         from .. import ops
         self._check(cols)
         p = self.plan
         Fp, Fc = p.widths(F, 4)
         self.ensure(Fp)
-        b = None
-        if bias is not None:
-            b = _pad_cols(bias.float().view(1, -1), Fp).view(-1)[p.col_slice(F)].contiguous()
+        b = _bias_slice(p, None if bias is None else bias.float(), F, 4)
         self._flip ^= 1
         off = self._r_off[self._flip]
         tab = self._table(('r', self._flip, Fc),
-                          [a + off + p.rank * Fc * 4 for a in self._peer])
+                          [self._peer[p.rg * p.Gc + j] + off + p.cg * Fc * 4
+                           for j in range(p.Gc)])
         ops.seg_gather_reduce_routed_raw(cols[:, :Fc], graph.adj.dst, graph.w_csr, b, tab, p.blk,
                                          Fp)
-        self.bytes_sent_total += (p.world_size - 1) * p.blk * Fc * 4
+        self.bytes_sent_total += (p.Gc - 1) * p.blk * Fc * 4
         self.fence()
         return self._view(off, p.blk, Fp)[:p.n_local]
+
+    def transform_to_cols(self, graph, rows, w, bias, F, relu, transform=None, out=None):
+        """``relu?(rows @ w + bias)`` with the epilogue of the GEMM storing the column
+        blocks straight into the column buffers of their ranks."""
+        from .. import ops
+        self._check(rows)
+        p = self.plan
+        Fp, Fc = p.widths(F, 4)
+        self.ensure(Fp)
+        if rows.size(0) > 0 and not ops._gemm_eligible(rows, w):
+            return self.rows_to_cols(ops.linear(rows, w, bias), F, relu)
+        if rows.size(0) > 0:
+            ops.gemm_xw_routed_raw(rows, w, bias, Fc, self._cols_table(), p.lo, Fc, relu, p.Gr)
+        self._sent_cols(Fc)
+        self.fence()
+        return self._view(self._c_off, p.n_padded, Fc)
 
     def rows_to_cols(self, rows, F, relu=False):
         from .. import ops
@@ -283,51 +348,62 @@ class PeerTransport(object):
         if rows.size(1) < Fp or rows.stride(1) != 1 or rows.stride(0) % 4 or \
                 rows.data_ptr() % 16:
             rows = _pad_cols(rows[:, :min(rows.size(1), Fp)], Fp)
-        tab = self._table(('c',), [a + self._c_off for a in self._peer])
         if rows.size(0) > 0:
-            ops.cols_scatter_raw(rows, Fc, p.world_size, tab, p.lo, Fc, relu)
-        self.bytes_sent_total += (p.world_size - 1) * p.n_local * Fc * 4
+            ops.cols_scatter_raw(rows, Fc, p.Gc, self._cols_table(), p.lo, Fc, relu, p.Gr)
+        self._sent_cols(Fc)
         self.fence()
         return self._view(self._c_off, p.n_padded, Fc)
 
     def cols_to_rows(self, cols, F):
-        """Pure redistribution (no aggregation): strided device copies into the peers."""
+        """Pure redistribution (no aggregation): strided device copies into the peers
+        of the same row group."""
         self._check(cols)
         p = self.plan
         Fp, Fc = p.widths(F, 4)
         self.ensure(Fp)
         self._flip ^= 1
         off = self._r_off[self._flip]
-        for q in range(p.world_size):
+        for j in range(p.Gc):
+            q = p.rg * p.Gc + j
             n = min(p.blk, max(p.num_nodes - q * p.blk, 0))
             if n == 0:
                 continue
             dst = torch.as_tensor(_DevMem(self._peer[q] + off, p.blk * Fp * 4), device=self.device)
             dst = dst.view(torch.float32).view(p.blk, Fp)
-            dst[:n, p.rank * Fc:(p.rank + 1) * Fc].copy_(cols[q * p.blk:q * p.blk + n, :Fc])
-        self.bytes_sent_total += (p.world_size - 1) * p.blk * Fc * 4
+            dst[:n, p.cg * Fc:(p.cg + 1) * Fc].copy_(cols[q * p.blk:q * p.blk + n, :Fc])
+        self.bytes_sent_total += (p.Gc - 1) * p.blk * Fc * 4
         self.fence()
         return self._view(off, p.blk, Fp)[:p.n_local]
 
 
 class SlicedGraph(object):
-    """The whole (loop-augmented, normalised) graph on every rank plus this rank's
-    row block / column slice bookkeeping."""
+    """The (loop-augmented, normalised) in-edges of this rank's row group — the whole
+    graph when there is one row group — plus the row block / column slice bookkeeping."""
 
     def __init__(self, edge_index, norm, num_nodes, rank, world_size, group=None, i=1,
-                 transport='peer', build_adj=True):
-        self.plan = SlicePlan(num_nodes, world_size, rank)
-        self.edge_index, self.norm, self.i = edge_index, norm, i
+                 transport='peer', build_adj=True, row_groups=1):
+        self.plan = p = SlicePlan(num_nodes, world_size, rank, row_groups)
+        self.i = i
         self.device = edge_index.device
+        if p.Gr > 1:                                   # in-edges of the row group, renumbered
+            t = edge_index[i]
+            mask = (t >= p.g_lo) & (t < p.g_hi)
+            ei = edge_index[:, mask].clone()
+            ei[i] -= p.g_lo
+            edge_index, norm = ei, (None if norm is None else norm[mask].contiguous())
+        self.edge_index, self.norm = edge_index, norm
+        self.num_edges_local = edge_index.size(1)
         self.adj = self.w_csr = None
         if build_adj:
             from ..graph import Adj
-            self.adj = Adj(edge_index, i, (num_nodes, num_nodes))
+            size = [0, 0]
+            size[i], size[1 - i] = p.n_group, num_nodes
+            self.adj = Adj(edge_index, i, size)
             self.w_csr = None if norm is None else self.adj.permuted(norm.float(), 'dst')
         if transport == 'peer':
-            self.transport = PeerTransport(self.plan, self.device, group)
+            self.transport = PeerTransport(p, self.device, group)
         elif transport == 'collective':
-            self.transport = CollectiveTransport(self.plan, group)
+            self.transport = CollectiveTransport(p, group)
         else:
             raise ValueError("transport must be 'peer' or 'collective'")
         self._bufs = {}
@@ -355,6 +431,25 @@ class SlicedGraph(object):
             self._bufs[key] = buf
         return buf
 
+    def padded(self, key, t, rows, cols):
+        """``t`` zero-padded to ``[rows, cols]`` (or ``[cols]``), cached per tensor version."""
+        if t is None:
+            return None
+        if tuple(t.shape) == ((rows, cols) if t.dim() == 2 else (cols,)):
+            return t
+        hit = self._bufs.get(key)
+        if hit is None or hit[0] is not t or hit[1] != t._version or \
+                hit[2].shape[-1] != cols or (t.dim() == 2 and hit[2].size(0) != rows):
+            d = t.detach()
+            out = d.new_zeros((rows, cols) if t.dim() == 2 else (cols,))
+            if t.dim() == 2:
+                out[:t.size(0), :t.size(1)] = d
+            else:
+                out[:t.numel()] = d
+            hit = (t, t._version, out)
+            self._bufs[key] = hit
+        return hit[2]
+
 
 def _native_aggregate(graph, cols, bias):
     from .. import ops
@@ -380,40 +475,49 @@ def sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols', aggregate=_
     """GCN forward with ``layers = [(weight [in,out], bias|None), ...]``; ReLU between
     layers when ``relu``.  ``x``: this rank's column slice ``[n_padded, Fc]``
     (``x_layout='cols'``, see ``SlicedGraph.slice_cols``) or its rows ``[n_local, in]``
-    (``'rows'``).  Returns this rank's rows ``[n_local, out]`` of the last layer."""
+    (``'rows'``).  Returns this rank's rows ``[n_local, out]`` of the last layer.
+
+    Every layer aggregates at ``min(in, out)`` channels (``A (X W) = (A X) W``).  The
+    forward is a chain of two primitives — aggregate (column layout -> row layout) and
+    transform (row layout -> row layout, or -> column layout when an aggregation follows:
+    then the layout change is fused into the GEMM epilogue)."""
     p, tr = graph.plan, graph.transport
-    state, kind = x, x_layout
     esz = x.element_size()
-
-    def padded_weight(k, w, rows):
-        if w.size(0) == rows:
-            return w
-        hit = graph._bufs.get(('w', k))
-        if hit is None or hit[0] is not w or hit[1] != w._version or hit[2].size(0) != rows:
-            hit = (w, w._version, _pad_rows(w.detach(), rows).contiguous())
-            graph._bufs[('w', k)] = hit
-        return hit[2]
-
+    ops_seq = []                                           # ('agg', F, bias, act) | ('gemm', k, w, b, act)
     for k, (w, b) in enumerate(layers):
-        fin, fout = w.shape
-        fp_in, _ = p.widths(fin, esz)
-        fp_out, _ = p.widths(fout, esz)
         act = bool(relu) and k + 1 < len(layers)
-        out = graph.buffer(('y', k), p.n_local, fp_out, w.dtype)
-        if fin <= fout:                                   # (A X) W: aggregate at width fin
+        if w.size(0) <= w.size(1):
+            ops_seq += [('agg', w.size(0), None, False), ('gemm', k, w, b, act)]
+        else:
+            ops_seq += [('gemm', k, w, None, False), ('agg', w.size(1), b, act)]
+    state, kind = x, x_layout
+    for n_op, op in enumerate(ops_seq):
+        if op[0] == 'agg':
+            _, F, b, act = op
             if kind == 'rows':
-                state = tr.rows_to_cols(state, fin, False)
-            rows = tr.aggregate_to_rows(graph, state, fin, None, aggregate)   # [n_local, fp_in]
-            state = transform(rows, padded_weight(k, w, fp_in), b, out, act)  # bias, ReLU fused
-        else:                                             # A (X W): aggregate at width fout
-            if kind == 'cols':
-                state = tr.cols_to_rows(state, fin)
-            t = transform(state, padded_weight(k, w, state.size(1)), None, out, False)
-            cols = tr.rows_to_cols(t, fout, False)
-            state = tr.aggregate_to_rows(graph, cols, fout, b, aggregate)     # bias fused
+                state = tr.rows_to_cols(state, F, False)
+            state = tr.aggregate_to_rows(graph, state, F, b, aggregate)      # bias fused
             if act:
                 state = torch.relu_(state)
-        kind = 'rows'
-    if kind == 'cols':                                    # no layers
+            kind = 'rows'
+        else:
+            _, k, w, b, act = op
+            fin, fout = w.shape
+            if kind == 'cols':
+                state = tr.cols_to_rows(state, fin)
+            fp_out, _ = p.widths(fout, esz)
+            wp = graph.padded(('w', k), w, state.size(1), fp_out)   # zero rows / columns: padding
+            bp = graph.padded(('b', k), b, 0, fp_out)
+            out = graph.buffer(('y', k), p.n_local, fp_out, w.dtype)
+            if n_op + 1 < len(ops_seq) and ops_seq[n_op + 1][0] == 'agg':
+                state = tr.transform_to_cols(graph, state, wp, bp, fout, act, transform, out)
+                kind = 'cols'
+            else:
+                state = transform(state, wp, bp, out, act)
+                kind = 'rows'
+    if not layers:
         return state
-    return state[:, :layers[-1][0].size(1)]
+    fout = layers[-1][0].size(1)
+    if kind == 'cols':
+        state = tr.cols_to_rows(state, fout)
+    return state[:, :fout]

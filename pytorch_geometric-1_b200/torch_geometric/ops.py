@@ -139,14 +139,33 @@ def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, re
              int(blk_rows), int(ldo), nat.ptr(ws), ws_bytes)
 
 
-def cols_scatter_raw(src, Fc, n_parts, dst_tab, dst_row0, ldd, relu=False):
+def cols_scatter_raw(src, Fc, n_parts, dst_tab, dst_row0, ldd, relu=False, n_dup=1):
     """Row layout -> column layout (pygb_cols_scatter): column block ``q`` of
-    ``src [n, n_parts*Fc]`` is stored at ``dst_tab[q] + (dst_row0 + r) * ldd``."""
+    ``src [n, n_parts*Fc]`` is stored at ``dst_tab[q*n_dup + d] + (dst_row0 + r) * ldd``
+    for every ``d < n_dup``."""
     dev = nat.require_cuda(src, dst_tab)
     assert src.dim() == 2 and src.stride(1) == 1 and src.size(1) >= Fc * n_parts
-    assert dst_tab.dtype == torch.int64 and dst_tab.numel() >= n_parts
+    assert dst_tab.dtype == torch.int64 and dst_tab.numel() >= n_parts * n_dup
     nat.call('pygb_cols_scatter', dev, nat.dtype_code(src), nat.ptr(src), _ld(src), src.size(0),
-             int(Fc), int(n_parts), nat.ptr(dst_tab), int(dst_row0), int(ldd), int(bool(relu)))
+             int(Fc), int(n_parts), int(n_dup), nat.ptr(dst_tab), int(dst_row0), int(ldd),
+             int(bool(relu)))
+
+
+def gemm_xw_routed_raw(x, w, bias, Fc, dst_tab, dst_row0, ldd, relu=False, n_dup=1, passes=None):
+    """``relu?(x @ w + bias)`` with the result's column blocks of ``Fc`` columns stored
+    through ``dst_tab`` (pygb_gemm_xw_routed): the row -> column layout change of the
+    feature-sliced multi-GPU forward fused into the GEMM epilogue."""
+    dev = nat.require_cuda(x, w, bias, dst_tab)
+    if not _gemm_eligible(x, w):
+        raise ValueError('gemm_xw_routed_raw: operands not eligible for the tcgen05 kernel')
+    M, K = x.shape
+    N = w.size(1)
+    assert N % Fc == 0 and dst_tab.dtype == torch.int64 and dst_tab.numel() >= N // Fc * n_dup
+    ws_bytes = nat.workspace('pygb_gemm_weight_workspace', K, N)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    nat.call('pygb_gemm_xw_routed', dev, nat.ptr(x), x.stride(0), M, K, nat.ptr(w), w.stride(0), N,
+             nat.ptr(_f32(bias)), int(bool(relu)), nat.ptr(dst_tab), int(Fc), int(n_dup),
+             int(dst_row0), int(ldd), int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
 
 
 def gather_rows_raw(x, index):

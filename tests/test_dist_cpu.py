@@ -120,7 +120,7 @@ def test_partition_plan_properties():
 
 # ---- feature-sliced layout (dist/sliced.py) ------------------------------------------
 def _sliced_oracle_aggregate(graph, cols, bias):
-    ei, n = graph.edge_index, graph.plan.num_nodes
+    ei, n = graph.edge_index, graph.plan.n_group        # in-edges of the rank's row group
     msg = graph.norm.view(-1, 1) * cols[ei[1 - graph.i]]
     out = O.scatter_('add', msg, ei[graph.i], 0, n)
     return out + bias if bias is not None else out
@@ -133,7 +133,7 @@ def _sliced_transform(x, weight, bias, out, relu=False):
     return out
 
 
-def _sliced_worker(rank, world, port, q, x_layout):
+def _sliced_worker(rank, world, port, q, x_layout, row_groups):
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
     dist.init_process_group('gloo', rank=rank, world_size=world)
@@ -147,9 +147,11 @@ def _sliced_worker(rank, world, port, q, x_layout):
         dims = [(10, 16), (16, 16), (16, 5), (5, 7)]   # (AX)W, (AX)W, A(XW), (AX)W
         layers = [(torch.randn(a, b) / a ** 0.5, torch.randn(b)) for a, b in dims]
         ei2, norm = O.gcn_norm(ei, n, dtype=torch.float32)
-        g = SlicedGraph(ei2, norm, n, rank, world, transport='collective', build_adj=False)
+        g = SlicedGraph(ei2, norm, n, rank, world, transport='collective', build_adj=False,
+                        row_groups=row_groups)
         pl = g.plan
         assert pl.n_padded >= n and pl.blk * (world - 1) < n
+        assert g.num_edges_local == int(((ei2[1] >= pl.g_lo) & (ei2[1] < pl.g_hi)).sum())
         xin = g.slice_cols(x) if x_layout == 'cols' else g.local_rows(x).contiguous()
         out_local = sliced_gcn_forward(g, xin, layers, relu=True, x_layout=x_layout,
                                        aggregate=_sliced_oracle_aggregate,
@@ -175,12 +177,14 @@ def _sliced_worker(rank, world, port, q, x_layout):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('world,x_layout', [(2, 'cols'), (2, 'rows'), (3, 'cols')])
-def test_sliced_gcn_gloo(world, x_layout):
+@pytest.mark.parametrize('world,x_layout,row_groups', [(2, 'cols', 1), (2, 'rows', 1),
+                                                       (3, 'cols', 1), (4, 'cols', 2),
+                                                       (2, 'rows', 2)])
+def test_sliced_gcn_gloo(world, x_layout, row_groups):
     ctx = mp.get_context('spawn')
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, x_layout))
+    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, x_layout, row_groups))
              for r in range(world)]
     for p in procs:
         p.start()
@@ -197,14 +201,21 @@ def test_sliced_gcn_gloo(world, x_layout):
 def test_slice_plan_properties():
     from torch_geometric.dist import SlicePlan
     for n in (2, 7, 301, 2449029):
-        for world in (1, 2, 3, 4, 8):
-            plans = [SlicePlan(n, world, r) for r in range(world)]
+        for world, gr in ((1, 1), (2, 1), (3, 1), (4, 1), (8, 1), (2, 2), (4, 2), (8, 2), (8, 4)):
+            plans = [SlicePlan(n, world, r, gr) for r in range(world)]
+            gc = world // gr
             assert sum(p.n_local for p in plans) == n
             assert all(p.lo == min(r * p.blk, n) for r, p in enumerate(plans))
+            # a row group is the union of the row blocks of its ranks
+            for p in plans:
+                mine = [q for q in plans if q.rg == p.rg]
+                assert p.g_lo == min(q.lo for q in mine) and p.g_hi == max(q.hi for q in mine)
+                assert p.rank == p.rg * gc + p.cg
+            assert sum(p.n_group for p in plans if p.cg == 0) == n
             for F in (1, 5, 47, 100, 256):
                 Fp, Fc = plans[0].widths(F, 4)
-                assert Fp >= F and Fp == Fc * world and Fc % 8 == 0 and Fp - F < 8 * world
-                cover = [plans[0].col_slice(F, 4, r) for r in range(world)]
+                assert Fp >= F and Fp == Fc * gc and Fc % 8 == 0 and Fp - F < 8 * gc
+                cover = [plans[0].col_slice(F, 4, c) for c in range(gc)]
                 assert cover[0].start == 0 and cover[-1].stop == Fp
     # exchange volume: P times less than the all-gather of the row partition
     p8 = SlicePlan(2449029, 8, 0)

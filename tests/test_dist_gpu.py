@@ -89,7 +89,7 @@ def test_dist_gcn_two_gpus_nccl():
 
 
 # ---- feature-sliced layout ---------------------------------------------------------
-def _sliced_worker(rank, world, port, q, transport, x_layout):
+def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for p in (root, os.path.join(root, 'pytorch_geometric-1_b200'), os.path.join(root, 'tests')):
@@ -112,7 +112,7 @@ def _sliced_worker(rank, world, port, q, transport, x_layout):
         dims = [(100, 256), (256, 256), (256, 47)]
         layers = [(torch.randn(a, b) / a ** 0.5, torch.randn(b)) for a, b in dims]
         ei2, norm = GCNConv.norm(ei.to(dev), n, None, False, torch.float32)
-        g = SlicedGraph(ei2, norm, n, rank, world, transport=transport)
+        g = SlicedGraph(ei2, norm, n, rank, world, transport=transport, row_groups=row_groups)
         pl = g.plan
         xin = g.slice_cols(x.to(dev)) if x_layout == 'cols' else g.local_rows(x.to(dev)).contiguous()
         lay = [(w.to(dev), b.to(dev)) for w, b in layers]
@@ -140,11 +140,11 @@ def _sliced_worker(rank, world, port, q, transport, x_layout):
         dist.destroy_process_group()
 
 
-def _run_sliced(world, transport, x_layout):
+def _run_sliced(world, transport, x_layout, row_groups=1):
     ctx = mp.get_context('spawn')
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, transport, x_layout))
+    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, transport, x_layout, row_groups))
              for r in range(world)]
     for p in procs:
         p.start()
@@ -156,12 +156,19 @@ def _run_sliced(world, transport, x_layout):
     assert err <= 2e-5, err
 
 
-@pytest.mark.parametrize('transport,x_layout', [('collective', 'cols'), ('peer', 'cols'),
-                                                ('peer', 'rows')])
-def test_sliced_gcn_two_gpus(transport, x_layout):
+@pytest.mark.parametrize('transport,x_layout,row_groups', [
+    ('collective', 'cols', 1), ('peer', 'cols', 1), ('peer', 'rows', 1), ('peer', 'cols', 2)])
+def test_sliced_gcn_two_gpus(transport, x_layout, row_groups):
     if torch.cuda.device_count() < 2:
         pytest.skip('needs two GPUs')
-    _run_sliced(2, transport, x_layout)
+    _run_sliced(2, transport, x_layout, row_groups)
+
+
+@pytest.mark.parametrize('transport', ['collective', 'peer'])
+def test_sliced_gcn_four_gpus_two_row_groups(transport):
+    if torch.cuda.device_count() < 4:
+        pytest.skip('needs four GPUs')
+    _run_sliced(4, transport, 'cols', 2)
 
 
 @pytest.mark.parametrize('transport', ['collective', 'peer'])
@@ -199,13 +206,36 @@ def test_routed_gather_reduce_and_cols_scatter(dev):
                        for b in bufs), 'stores outside the slice'
     finally:
         ops.STREAM_T = old
-    # column scatter: [n, 3*8] -> three [n0 + n, 8] buffers, with and without relu
+    # column scatter: [n, 3*8] -> 3 column blocks x 2 copies of [n0 + n, 8], with / without relu
     src = torch.randn(n, 28, generator=g).to(dev)
     for relu in (False, True):
-        outs = [torch.full((n + 5, 12), -7.0, device=dev) for _ in range(3)]
+        outs = [torch.full((n + 5, 12), -7.0, device=dev) for _ in range(6)]
         tab = torch.tensor([o.data_ptr() for o in outs], dtype=torch.int64).to(dev)
-        ops.cols_scatter_raw(src, 8, 3, tab, 5, 12, relu)
-        for q_, o in enumerate(outs):
+        ops.cols_scatter_raw(src, 8, 3, tab, 5, 12, relu, n_dup=2)
+        for k_, o in enumerate(outs):
+            q_ = k_ // 2
             want = src[:, q_ * 8:(q_ + 1) * 8]
             assert torch.equal(o[5:, :8], torch.relu(want) if relu else want)
             assert float(o[:5].max()) == -7.0 and float(o[:, 8:].max()) == -7.0
+
+
+@pytest.mark.parametrize('M,K,N,Fc,dup', [(1000, 104, 256, 32, 1), (777, 256, 64, 8, 2),
+                                           (130, 64, 48, 24, 1), (5, 16, 16, 16, 4)])
+def test_gemm_routed_epilogue(dev, M, K, N, Fc, dup):
+    """pygb_gemm_xw_routed == pygb_gemm_xw followed by the column scatter, bit for bit."""
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(M + N)
+    x = torch.randn(M, K, generator=g).to(dev)
+    w = (torch.randn(K, N, generator=g) / K ** 0.5).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    for relu in (False, True):
+        plain = ops.gemm_xw_raw(x, w, b, relu=relu)
+        nblk, row0, ldd = N // Fc, 3, Fc + 4
+        outs = [torch.full((M + row0 + 2, ldd), -7.0, device=dev) for _ in range(nblk * dup)]
+        tab = torch.tensor([o.data_ptr() for o in outs], dtype=torch.int64).to(dev)
+        ops.gemm_xw_routed_raw(x, w, b, Fc, tab, row0, ldd, relu=relu, n_dup=dup)
+        for k_, o in enumerate(outs):
+            q_ = k_ // dup
+            assert torch.equal(o[row0:row0 + M, :Fc], plain[:, q_ * Fc:(q_ + 1) * Fc])
+            assert float(o[:row0].max()) == -7.0 and float(o[row0 + M:].max()) == -7.0
+            assert float(o[:, Fc:].max()) == -7.0
