@@ -147,6 +147,9 @@ class CollectiveTransport(object):
         self.collectives += 1
         return recv
 
+    def prepare(self, fp_max):
+        pass
+
     def group_cols_to_rows(self, z, F):
         """z [n_group, Fc]: this rank's column slice of the rows of its row group ->
         rows [n_local, Fp].  Only the ranks of the same row group exchange data."""
@@ -220,8 +223,13 @@ class PeerTransport(object):
         c_bytes = (p.n_padded * (fp_max // p.Gc) * 4 + 255) // 256 * 256
         return r_bytes, c_bytes
 
+    def prepare(self, fp_max):
+        if fp_max > 0:
+            self.ensure(fp_max)
+
     def ensure(self, fp_max):
-        """Collective: (re)allocate the arena for row widths up to ``fp_max`` fp32 columns."""
+        """Collective: (re)allocate the arena for row widths up to ``fp_max`` fp32 columns.
+        Invalidates every view handed out before: call it (``prepare``) ahead of a forward."""
         if self._cap is not None and fp_max <= self._cap:
             return
         nat, p = self.nat, self.plan
@@ -490,6 +498,9 @@ def sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols', aggregate=_
             ops_seq += [('agg', w.size(0), None, False), ('gemm', k, w, b, act)]
         else:
             ops_seq += [('gemm', k, w, None, False), ('agg', w.size(1), b, act)]
+    # size the peer arena once, before any view of it exists (a later, wider layer must not
+    # re-allocate it under a live row buffer)
+    tr.prepare(max([p.widths(f, esz)[0] for w, _ in layers for f in w.shape] or [0]))
     state, kind = x, x_layout
     for n_op, op in enumerate(ops_seq):
         if op[0] == 'agg':
