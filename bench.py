@@ -393,7 +393,7 @@ def run_b200(args):
         if name in K1_NAMES:
             key += ':F=%d' % a[4]
         elif name in ('pygb_gemm_xw', 'pygb_gemm_xw_routed'):
-            key += ':K=%d,N=%d' % (a[3], a[6])
+            key += ':K=%d,N=%d' % (a[5], a[8])
         breakdown[key] = breakdown.get(key, 0.0) + e0.elapsed_time(e1) / args.steps
     breakdown = {k: round(v, 4) for k, v in breakdown.items()}
     breakdown['other (framework elementwise ops, fences, waiting on peers)'] = round(

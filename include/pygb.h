@@ -167,15 +167,19 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
  * where out_tab is a DEVICE array of ceil(n_rows / blk_rows) base pointers, one
  * per block of destination rows — local memory or peer-GPU memory opened with
  * pygb_peer_open (plain stores over NVLink; the caller orders them against the
- * consumer with a stream-ordered collective).  All bases 16-byte aligned. */
+ * consumer with a stream-ordered collective).  All bases 16-byte aligned.
+ * sub_rot rotates the work order: the launch starts at sub-item sub_rot (slot
+ * sub_rot * Ts) and wraps around, so that ranks writing to each other begin at
+ * different row blocks and no peer receives from everybody at once; the result
+ * does not depend on it. */
 int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, int64_t ldx,
                                          int64_t F, const int32_t* rowptr,
                                          const int32_t* idx_flagged, const float* edge_w,
                                          const float* bias, int64_t n_rows, int64_t E,
                                          const int32_t* nz_rows, const int32_t* sub_info,
                                          int32_t Ts, int64_t n_sub, void* const* out_tab,
-                                         int64_t blk_rows, int64_t ldo, void* ws,
-                                         size_t ws_bytes, pygb_stream_t s);
+                                         int64_t blk_rows, int64_t sub_rot, int64_t ldo,
+                                         void* ws, size_t ws_bytes, pygb_stream_t s);
 
 /* Same walk with a per-(edge, head) weight: out[i,h,:] = sum_p
  * head_w[wp(p)*H + h] * x[idx[p],h,:], wp(p) = wperm ? wperm[p] : p — GAT's
@@ -292,11 +296,16 @@ int pygb_gat_edge_grad(const float* xw, int64_t ldx, const float* a_src,
  * lda % 4 == 0 (else PYGB_E_UNSUPPORTED: the caller uses its library GEMM).  `ws`
  * holds the split, transposed copy of W (pygb_gemm_weight_workspace bytes).
  * relu != 0 applies max(x, 0) after the bias in the epilogue (the activation
- * between two layers when the caller owns the whole forward, dist/sliced.py). */
+ * between two layers when the caller owns the whole forward, dist/sliced.py).
+ * a_slices > 1: A is stored as a_slices planes of [M, K/a_slices] columns (row
+ * stride lda, plane stride a_plane elements; K/a_slices a multiple of 32) — the
+ * slice-major row buffer the aggregation kernels of the column-slice ranks fill
+ * with contiguous stores; a_slices = 1: ordinary row-major A. */
 size_t pygb_gemm_weight_workspace(int64_t K, int64_t N);
-int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
-                 int64_t ldw, int64_t N, const float* bias, int relu, float* C,
-                 int64_t ldc, int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
+int pygb_gemm_xw(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane, int64_t M,
+                 int64_t K, const float* W, int64_t ldw, int64_t N, const float* bias,
+                 int relu, float* C, int64_t ldc, int passes, void* ws, size_t ws_bytes,
+                 pygb_stream_t s);
 
 /* pygb_gemm_xw with the row layout -> column layout redistribution of the
  * feature-sliced multi-GPU layout fused into the epilogue: N is
@@ -305,8 +314,9 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float*
  * dst_tab a DEVICE array of (N/Fc) * n_dup base pointers, local or peer-GPU memory
  * (pygb_peer_open): the tiles leave over NVLink while the main loop of the next
  * tile runs.  Fc and ldd multiples of 4, bases 16-byte aligned, n_dup <= 4. */
-int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
-                        int64_t ldw, int64_t N, const float* bias, int relu,
+int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane,
+                        int64_t M, int64_t K, const float* W, int64_t ldw, int64_t N,
+                        const float* bias, int relu,
                         float* const* dst_tab, int64_t Fc, int32_t n_dup, int64_t dst_row0,
                         int64_t ldd, int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
 

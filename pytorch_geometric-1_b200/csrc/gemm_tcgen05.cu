@@ -77,6 +77,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                            int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tcgen05_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -143,6 +151,7 @@ struct GemmParams {
   float* C;
   int64_t ldc;
   int M, N, K;
+  int a_kw;       // columns per plane of A (K when A is one row-major matrix)
   int BN;         // N tile (multiple of 16, <= 256)
   int stages;     // 2..4
   int tmem_cols;  // power of two >= 2*BN (two accumulator buffers)
@@ -222,7 +231,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           const uint32_t ph = (uint32_t)(it / S) & 1u;
           mbar_wait(empty(s), ph ^ 1u);
           mbar_expect_tx(full(s), kATileBytes + (PASSES == 3 ? 2 : 1) * b_bytes);
-          tma_load_2d(a_hi(s), &mapA, full(s), kt * kBK, m0);
+          {  // A is a_slices planes of [M, a_kw] columns (one plane: ordinary row-major)
+            const int kcol = kt * kBK, sl = kcol / P.a_kw;
+            tma_load_3d(a_hi(s), &mapA, full(s), kcol - sl * P.a_kw, m0, sl);
+          }
           tma_load_2d(b_hi(s), &mapBh, full(s), kt * kBK, n0);
           if (PASSES == 3) tma_load_2d(b_lo(s), &mapBl, full(s), kt * kBK, n0);
         }
@@ -445,6 +457,29 @@ int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int
   return PYGB_OK;
 }
 
+// A as `slices` planes of [rows, cols] (row stride ld, plane stride `plane` elements).
+int make_map_a(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld,
+               int64_t slices, int64_t plane) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled is not available from the driver");
+    return PYGB_E_UNSUPPORTED;
+  }
+  cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)slices};
+  cuuint64_t strides[2] = {(cuuint64_t)ld * 4, (cuuint64_t)(slices > 1 ? plane : ld * rows) * 4};
+  cuuint32_t box[3] = {(cuuint32_t)kBK, (cuuint32_t)kBM, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(ptr), dims, strides,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) for A [%lld x %lld x %lld] ld %lld", (int)r,
+              (long long)slices, (long long)rows, (long long)cols, (long long)ld);
+    return PYGB_E_CUDA;
+  }
+  return PYGB_OK;
+}
+
 inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 
 }  // namespace
@@ -464,14 +499,20 @@ struct GemmRoute {
   int64_t fc, dup, row0, ldd;
 };
 
-static int gemm_xw_impl(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
+static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane, int64_t M,
+                        int64_t K, const float* W,
                         int64_t ldw, int64_t N, const float* bias, int relu, float* C,
                         int64_t ldc, const GemmRoute* route, int passes, void* ws,
                         size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(M >= 0 && K > 0 && N > 0 && M < (1ll << 31) - 256 && K < (1 << 20) && N < (1 << 20),
                "pygb_gemm_xw: bad sizes");
   PYGB_REQUIRE(passes == 1 || passes == 3, "pygb_gemm_xw: passes must be 1 (tf32) or 3 (3xtf32)");
-  PYGB_REQUIRE(lda >= K && ldw >= N && ldc >= N, "pygb_gemm_xw: bad leading dimensions");
+  PYGB_REQUIRE(a_slices >= 1 && K % a_slices == 0, "pygb_gemm_xw: K must be a_slices planes");
+  const int64_t a_kw = K / a_slices;
+  PYGB_REQUIRE(lda >= a_kw && ldw >= N && ldc >= N, "pygb_gemm_xw: bad leading dimensions");
+  PYGB_REQUIRE(a_slices == 1 || (a_kw % kBK == 0 && a_plane >= lda * M && a_plane % 4 == 0),
+               "pygb_gemm_xw: sliced A needs %d-column multiples per plane and a 16-byte "
+               "aligned plane stride", kBK);
   if (M == 0) return PYGB_OK;
   PYGB_REQUIRE(A && W && (C || route) && ws, "pygb_gemm_xw: null pointer");
   if (!aligned16(A) || (lda % 4) != 0) {
@@ -508,6 +549,7 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t M, int64_t K, const
   P.M = (int)M;
   P.N = (int)N;
   P.K = (int)K;
+  P.a_kw = (int)a_kw;
   P.BN = Np < 256 ? Np : 256;
   int tc = 32;
   while (tc < 2 * P.BN) tc <<= 1;
@@ -526,7 +568,7 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t M, int64_t K, const
   const size_t smem = stages * stage_bytes + kEpiBytes + 1024;
 
   CUtensorMap mapA, mapBh, mapBl;
-  int rc = make_map(&mapA, A, M, K, lda, kBM);
+  int rc = make_map_a(&mapA, A, M, a_kw, lda, a_slices, a_plane);
   if (rc) return rc;
   rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN);
   if (rc) return rc;
@@ -554,16 +596,17 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t M, int64_t K, const
   return PYGB_OK;
 }
 
-int pygb_gemm_xw(const float* A, int64_t lda, int64_t M, int64_t K, const float* W, int64_t ldw,
-                 int64_t N, const float* bias, int relu, float* C, int64_t ldc, int passes,
-                 void* ws, size_t ws_bytes, pygb_stream_t s) {
+int pygb_gemm_xw(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane, int64_t M,
+                 int64_t K, const float* W, int64_t ldw, int64_t N, const float* bias, int relu,
+                 float* C, int64_t ldc, int passes, void* ws, size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(C || M == 0, "pygb_gemm_xw: null pointer");
-  return gemm_xw_impl(A, lda, M, K, W, ldw, N, bias, relu, C, ldc, nullptr, passes, ws, ws_bytes,
-                      s);
+  return gemm_xw_impl(A, lda, a_slices, a_plane, M, K, W, ldw, N, bias, relu, C, ldc, nullptr,
+                      passes, ws, ws_bytes, s);
 }
 
-int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t M, int64_t K, const float* W,
-                        int64_t ldw, int64_t N, const float* bias, int relu,
+int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane, int64_t M,
+                        int64_t K, const float* W, int64_t ldw, int64_t N, const float* bias,
+                        int relu,
                         float* const* dst_tab, int64_t Fc, int32_t n_dup, int64_t dst_row0,
                         int64_t ldd, int passes, void* ws, size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(dst_tab && Fc > 0 && Fc % 4 == 0 && N % Fc == 0 && n_dup >= 1 && n_dup <= kMaxDup &&
@@ -571,8 +614,8 @@ int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t M, int64_t K, const
                "pygb_gemm_xw_routed: N must be a whole number of column blocks of Fc (multiple "
                "of 4) columns, 1 <= n_dup <= %d", kMaxDup);
   GemmRoute r{dst_tab, Fc, n_dup, dst_row0, ldd};
-  return gemm_xw_impl(A, lda, M, K, W, ldw, N, bias, relu, nullptr, N, &r, passes, ws, ws_bytes,
-                      s);
+  return gemm_xw_impl(A, lda, a_slices, a_plane, M, K, W, ldw, N, bias, relu, nullptr, N, &r,
+                      passes, ws, ws_bytes, s);
 }
 
 }  // extern "C"

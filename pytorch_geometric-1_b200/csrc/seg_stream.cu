@@ -66,6 +66,7 @@ struct StreamParams {
   void* const* out_tab;
   int blk_rows;
   unsigned blk_magic;  // floor(2^32 / blk_rows) + 1
+  int sub_rot;         // first sub-item this launch starts at (work order rotation)
   int64_t out_off;  // bytes
 };
 
@@ -119,7 +120,12 @@ seg_stream_kernel(const StreamParams P) {
 #pragma unroll
     for (int i = 0; i < KV; ++i) acc[v][i] = 0.f;
 
-  for (int item = blockIdx.x + gridDim.x * warp; item < n_items; item += W) {
+  // rotated start (routed output): ranks begin at different row blocks so that no peer
+  // receives from everybody at once
+  const int item_rot = (P.sub_rot / EPW) % (n_items > 0 ? n_items : 1);
+  for (int it = blockIdx.x + gridDim.x * warp; it < n_items; it += W) {
+    int item = it + item_rot;
+    if (item >= n_items) item -= n_items;
     // ---- per lane-group stream state ------------------------------------------------
     const int s = item * EPW + es;
     const bool live = s < P.n_sub;
@@ -507,8 +513,8 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
                            const int32_t* rowptr, const int32_t* idx_flagged, const float* edge_w,
                            const float* bias, int64_t n_rows, int64_t E, const int32_t* nz_rows,
                            const int32_t* sub_info, int32_t Ts, int64_t n_sub, void* out,
-                           void* const* out_tab, int64_t blk_rows, int64_t ldo, void* ws,
-                           size_t ws_bytes, pygb_stream_t s) {
+                           void* const* out_tab, int64_t blk_rows, int64_t sub_rot, int64_t ldo,
+                           void* ws, size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(reduce == PYGB_SUM || reduce == PYGB_MEAN,
                "pygb_seg_gather_reduce_stream: bad reduce %d", reduce);
   PYGB_REQUIRE(dtype == PYGB_F32 || dtype == PYGB_BF16,
@@ -521,6 +527,7 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
   if (n_rows == 0 || F == 0) return PYGB_OK;
   PYGB_REQUIRE(rowptr && (out || out_tab) && (E == 0 || (x && idx_flagged && nz_rows && sub_info)),
                "pygb_seg_gather_reduce_stream: null pointer");
+  PYGB_REQUIRE(sub_rot >= 0 && sub_rot <= n_sub, "pygb_seg_gather_reduce_stream_routed: bad sub_rot");
   PYGB_REQUIRE(!out_tab || (blk_rows > 1 && blk_rows < (1ll << 31)),
                "pygb_seg_gather_reduce_stream_routed: bad blk_rows");
   const int esz = dtype == PYGB_F32 ? 4 : 2;
@@ -558,6 +565,7 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
     P.out_tab = out_tab;
     P.blk_rows = (int)blk_rows;
     P.blk_magic = out_tab ? (unsigned)((1ull << 32) / (uint64_t)blk_rows + 1) : 0u;
+    P.sub_rot = (int)sub_rot;
     P.out_off = f0 * esz;
     P.ldo = ldo;
     P.sub_info = sub_info;
@@ -582,7 +590,7 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
                                   size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(out || n_rows == 0 || F == 0, "pygb_seg_gather_reduce_stream: null pointer");
   return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
-                         nz_rows, sub_info, Ts, n_sub, out, nullptr, 0, ldo, ws, ws_bytes, s);
+                         nz_rows, sub_info, Ts, n_sub, out, nullptr, 0, 0, ldo, ws, ws_bytes, s);
 }
 
 int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, int64_t ldx,
@@ -591,13 +599,13 @@ int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, i
                                          const float* bias, int64_t n_rows, int64_t E,
                                          const int32_t* nz_rows, const int32_t* sub_info,
                                          int32_t Ts, int64_t n_sub, void* const* out_tab,
-                                         int64_t blk_rows, int64_t ldo, void* ws, size_t ws_bytes,
-                                         pygb_stream_t s) {
+                                         int64_t blk_rows, int64_t sub_rot, int64_t ldo, void* ws,
+                                         size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(out_tab || n_rows == 0 || F == 0,
                "pygb_seg_gather_reduce_stream_routed: null pointer table");
   return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
-                         nz_rows, sub_info, Ts, n_sub, nullptr, out_tab, blk_rows, ldo, ws,
-                         ws_bytes, s);
+                         nz_rows, sub_info, Ts, n_sub, nullptr, out_tab, blk_rows, sub_rot, ldo,
+                         ws, ws_bytes, s);
 }
 
 }  // extern "C"

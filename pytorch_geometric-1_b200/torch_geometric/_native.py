@@ -43,15 +43,15 @@ SIGNATURES = {
     'pygb_seg_gather_reduce_stream': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P, _I,
                                            _L, _P, _L, _P, _Z, _P]),
     'pygb_seg_gather_reduce_stream_routed': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P,
-                                                  _I, _L, _P, _L, _L, _P, _Z, _P]),
+                                                  _I, _L, _P, _L, _L, _L, _P, _Z, _P]),
     'pygb_peer_alloc': (_I, [_Z, _P]),
     'pygb_peer_free': (_I, [_P]),
     'pygb_peer_export': (_I, [_P, _P, _Z]),
     'pygb_peer_open': (_I, [_P, _Z, _P]),
     'pygb_peer_close': (_I, [_P]),
     'pygb_cols_scatter': (_I, [_I, _P, _L, _L, _L, _I, _I, _P, _L, _L, _I, _P]),
-    'pygb_gemm_xw_routed': (_I, [_P, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _L, _L, _I, _P,
-                                 _Z, _P]),
+    'pygb_gemm_xw_routed': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _L, _L, _I,
+                                 _P, _Z, _P]),
     'pygb_seg_gather_reduce_heads': (_I, [_I, _P, _L, _I, _I, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
     'pygb_gather_rows': (_I, [_I, _P, _L, _L, _P, _L, _P, _L, _P]),
     'pygb_seg_max': (_I, [_I, _P, _L, _L, _P, _P, _P, _L, _L, _F, _I, _P, _L, _P, _P]),
@@ -65,7 +65,7 @@ SIGNATURES = {
                                      _P, _P, _L, _P, _P, _P, _Z, _P]),
     'pygb_gat_alpha': (_I, [_P, _P, _I, _F, _P, _P, _P, _L, _P, _P, _P, _P]),
     'pygb_gemm_weight_workspace': (_Z, [_L, _L]),
-    'pygb_gemm_xw': (_I, [_P, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _P, _Z, _P]),
+    'pygb_gemm_xw': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _P, _Z, _P]),
     'pygb_gat_edge_grad': (_I, [_P, _L, _P, _P, _I, _I, _F, _P, _P, _P, _L, _P, _L, _P, _P, _L,
                                 _P, _P, _P, _P, _P]),
 }

@@ -109,13 +109,16 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
     return out
 
 
-def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, reduce='sum'):
+def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, reduce='sum',
+                                 start_row=0):
     """The streaming fused gather-reduce with a routed output: row ``r`` of the
     result is stored at ``out_tab[r // blk_rows] + (r % blk_rows) * ldo`` (element
     units of ``x.dtype``) — ``out_tab`` is an int64 CUDA tensor of base addresses,
     local or peer-GPU (pygb_seg_gather_reduce_stream_routed; feature-sliced
-    multi-GPU aggregation, dist/sliced.py).  Nothing is returned: the caller owns
-    the destinations and orders the stores against their consumers."""
+    multi-GPU aggregation, dist/sliced.py).  ``start_row``: the launch begins its work
+    at (the work item holding) that destination row and wraps around — ranks that
+    store into each other start at different row blocks.  Nothing is returned: the
+    caller owns the destinations and orders the stores against their consumers."""
     dev = nat.require_cuda(x, w_csr, bias, out_tab)
     x2 = _rows2d(x)
     F = x2.size(1)
@@ -130,13 +133,21 @@ def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, re
     dt = nat.dtype_code(x2)
     Ts, n_sub, nz_rows, sub_info = csr.items(STREAM_T)
     idxf = csr.flagged('col')
+    sub_rot = 0
+    if start_row:
+        key = ('slot_of_row', int(start_row))
+        slot = csr._items.get(key)
+        if slot is None:
+            slot = int(csr.rowptr[min(int(start_row), csr.n_rows)].item())   # once per CSR
+            csr._items[key] = slot
+        sub_rot = min(slot // Ts, n_sub)
     ws_bytes = nat.workspace('pygb_seg_stream_workspace', dt, n_sub, F)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     nat.call('pygb_seg_gather_reduce_stream_routed', dev,
              nat.MEAN if reduce == 'mean' else nat.SUM, dt, nat.ptr(x2), _ld(x2), F,
              nat.ptr(csr.rowptr), nat.ptr(idxf), nat.ptr(_f32(w_csr)), nat.ptr(_f32(bias)),
              csr.n_rows, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub, nat.ptr(out_tab),
-             int(blk_rows), int(ldo), nat.ptr(ws), ws_bytes)
+             int(blk_rows), int(sub_rot), int(ldo), nat.ptr(ws), ws_bytes)
 
 
 def cols_scatter_raw(src, Fc, n_parts, dst_tab, dst_row0, ldd, relu=False, n_dup=1):
@@ -151,21 +162,25 @@ def cols_scatter_raw(src, Fc, n_parts, dst_tab, dst_row0, ldd, relu=False, n_dup
              int(bool(relu)))
 
 
-def gemm_xw_routed_raw(x, w, bias, Fc, dst_tab, dst_row0, ldd, relu=False, n_dup=1, passes=None):
+def gemm_xw_routed_raw(x, w, bias, Fc, dst_tab, dst_row0, ldd, relu=False, n_dup=1, passes=None,
+                       rows=None):
     """``relu?(x @ w + bias)`` with the result's column blocks of ``Fc`` columns stored
     through ``dst_tab`` (pygb_gemm_xw_routed): the row -> column layout change of the
-    feature-sliced multi-GPU forward fused into the GEMM epilogue."""
+    feature-sliced multi-GPU forward fused into the GEMM epilogue.  ``x`` as in
+    ``gemm_xw_raw``."""
     dev = nat.require_cuda(x, w, bias, dst_tab)
     if not _gemm_eligible(x, w):
         raise ValueError('gemm_xw_routed_raw: operands not eligible for the tcgen05 kernel')
-    M, K = x.shape
+    a_ptr, lda, a_slices, a_plane, M, K = _gemm_a_args(x, rows)
     N = w.size(1)
+    assert w.size(0) == K
     assert N % Fc == 0 and dst_tab.dtype == torch.int64 and dst_tab.numel() >= N // Fc * n_dup
     ws_bytes = nat.workspace('pygb_gemm_weight_workspace', K, N)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    nat.call('pygb_gemm_xw_routed', dev, nat.ptr(x), x.stride(0), M, K, nat.ptr(w), w.stride(0), N,
-             nat.ptr(_f32(bias)), int(bool(relu)), nat.ptr(dst_tab), int(Fc), int(n_dup),
-             int(dst_row0), int(ldd), int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
+    nat.call('pygb_gemm_xw_routed', dev, a_ptr, lda, a_slices, a_plane, M, K, nat.ptr(w),
+             w.stride(0), N, nat.ptr(_f32(bias)), int(bool(relu)), nat.ptr(dst_tab), int(Fc),
+             int(n_dup), int(dst_row0), int(ldd), int(passes or GEMM_PASSES), nat.ptr(ws),
+             ws_bytes)
 
 
 def gather_rows_raw(x, index):
@@ -508,19 +523,36 @@ def _pad4(n, itemsize):
 
 
 def _gemm_eligible(x, w):
-    return (GEMM_PASSES in (1, 3) and x.is_cuda and x.dim() == 2 and w.dim() == 2
-            and x.dtype == torch.float32 and w.dtype == torch.float32 and x.size(0) > 0
-            and x.size(1) > 0 and w.size(1) > 0 and x.stride(1) == 1 and x.stride(0) % 4 == 0
-            and x.stride(0) >= x.size(1) and x.data_ptr() % 16 == 0 and w.stride(1) == 1)
+    """2-D fp32 CUDA operands with 16-byte aligned rows; ``x`` may also be slice-major:
+    ``[S, M, Kc]`` planes of ``Kc`` (multiple of 32) columns, standing for ``[M, S*Kc]``."""
+    ok = (GEMM_PASSES in (1, 3) and x.is_cuda and w.dim() == 2
+          and x.dtype == torch.float32 and w.dtype == torch.float32 and x.size(-2) > 0
+          and x.size(-1) > 0 and w.size(1) > 0 and x.stride(-1) == 1 and x.stride(-2) % 4 == 0
+          and x.stride(-2) >= x.size(-1) and x.data_ptr() % 16 == 0 and w.stride(1) == 1)
+    if x.dim() == 3:
+        return (ok and x.size(2) % 32 == 0 and x.stride(0) % 4 == 0
+                and x.stride(0) >= x.stride(1) * x.size(1))
+    return ok and x.dim() == 2
 
 
-def gemm_xw_raw(x, w, bias=None, passes=None, out=None, relu=False):
+def _gemm_a_args(x, rows=None):
+    """(ptr, lda, a_slices, a_plane, M, K) of a row-major or slice-major A operand."""
+    if x.dim() == 3:
+        M = x.size(1) if rows is None else int(rows)
+        return nat.ptr(x), x.stride(1), x.size(0), x.stride(0), M, x.size(0) * x.size(2)
+    M = x.size(0) if rows is None else int(rows)
+    return nat.ptr(x), x.stride(0), 1, 0, M, x.size(1)
+
+
+def gemm_xw_raw(x, w, bias=None, passes=None, out=None, relu=False, rows=None):
     """``x @ w (+ bias)`` by the tcgen05 kernel; the result's rows are padded to 16 bytes
     (a view ``[:, :N]`` is returned) so that a following aggregation stays vectorised.
-    ``out``: optional ``[M, >=N]`` fp32 destination with unit inner stride (written in place)."""
+    ``out``: optional ``[M, >=N]`` fp32 destination with unit inner stride (written in place).
+    ``x``: ``[M, K]`` or slice-major ``[S, >=M, K/S]`` (``rows`` = M)."""
     dev = nat.require_cuda(x, w, bias)
-    M, K = x.shape
+    a_ptr, lda, a_slices, a_plane, M, K = _gemm_a_args(x, rows)
     N = w.size(1)
+    assert w.size(0) == K
     if out is None:
         ldc = _pad4(N, 4)
         out_full = torch.empty((M, ldc), dtype=torch.float32, device=dev)
@@ -531,7 +563,7 @@ def gemm_xw_raw(x, w, bias=None, passes=None, out=None, relu=False):
     ws_bytes = nat.workspace('pygb_gemm_weight_workspace', K, N)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     b = _f32(bias)
-    nat.call('pygb_gemm_xw', dev, nat.ptr(x), x.stride(0), M, K, nat.ptr(w), w.stride(0), N,
+    nat.call('pygb_gemm_xw', dev, a_ptr, lda, a_slices, a_plane, M, K, nat.ptr(w), w.stride(0), N,
              nat.ptr(b), int(bool(relu)), nat.ptr(out_full), ldc, int(passes or GEMM_PASSES),
              nat.ptr(ws), ws_bytes)
     return out_full[:, :N] if out_full.size(1) != N else out_full

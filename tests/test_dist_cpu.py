@@ -214,7 +214,7 @@ def test_slice_plan_properties():
             assert sum(p.n_group for p in plans if p.cg == 0) == n
             for F in (1, 5, 47, 100, 256):
                 Fp, Fc = plans[0].widths(F, 4)
-                assert Fp >= F and Fp == Fc * gc and Fc % 8 == 0 and Fp - F < 8 * gc
+                assert Fp >= F and Fp == Fc * gc and Fc % 8 == 0 and Fp - F < 32 * gc
                 cover = [plans[0].col_slice(F, 4, c) for c in range(gc)]
                 assert cover[0].start == 0 and cover[-1].stop == Fp
     # exchange volume: P times less than the all-gather of the row partition

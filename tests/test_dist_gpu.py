@@ -202,6 +202,10 @@ def test_routed_gather_reduce_and_cols_scatter(dev):
             ops.seg_gather_reduce_routed_raw(x, adj.dst, adj.permuted(w, 'dst'), bias, tab, blk, ldo)
             got = torch.cat([b[:, 8:8 + F] for b in bufs])[:n]
             assert_close(got, ref, 1e-6, 'routed rows')
+            for start in (1, 300, 450, n - 1):           # rotated work order: same bits
+                ops.seg_gather_reduce_routed_raw(x, adj.dst, adj.permuted(w, 'dst'), bias, tab,
+                                                 blk, ldo, start_row=start)
+                assert torch.equal(torch.cat([b[:, 8:8 + F] for b in bufs])[:n], got)
             assert all(float(b[:, :8].min()) == -7.0 and float(b[:, 8 + F:].max()) == -7.0
                        for b in bufs), 'stores outside the slice'
     finally:

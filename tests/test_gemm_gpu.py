@@ -47,6 +47,23 @@ def test_gemm_fused_relu_and_padded_output(dev, M, K, N):
     assert float(out[:, N:].max()) == -7.0 and float(out[:, N:].min()) == -7.0
 
 
+@pytest.mark.parametrize('M,S,Kc,N', [(1000, 4, 32, 256), (777, 2, 64, 48), (129, 8, 32, 16)])
+def test_gemm_slice_major_operand(dev, M, S, Kc, N):
+    """A stored as S planes of [rows, Kc] columns (3-D TMA map) == the row-major product,
+    bit for bit; rows of the planes beyond M are never read into the result."""
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(S * Kc)
+    x = torch.randn(M, S * Kc, generator=g).to(dev)
+    w = (torch.randn(S * Kc, N, generator=g) / (S * Kc) ** 0.5).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    planes = torch.full((S, M + 37, Kc), float('nan'), device=dev)
+    planes[:, :M] = x.view(M, S, Kc).permute(1, 0, 2)
+    assert ops._gemm_eligible(planes, w)
+    ref = ops.gemm_xw_raw(x, w, b, relu=True)
+    got = ops.gemm_xw_raw(planes, w, b, relu=True, rows=M)
+    assert got.shape == (M, N) and torch.equal(got, ref)
+
+
 @pytest.mark.parametrize('M,K,N', SHAPES[:5])
 def test_gemm_tf32_single_pass(dev, M, K, N):
     from torch_geometric import ops
