@@ -276,6 +276,7 @@ def run_b200(args):
                             transport='peer' if peer else 'collective', row_groups=row_groups)
         del ei_full, norm_full
         x_in = graph.slice_cols(x_dev)                  # this rank's columns of all rows
+        x_rows = graph.local_rows(x_dev).contiguous()   # e2e: every rank uploads its rows only
         n_rows_local = n
         del edge_index, x_dev
         torch.cuda.empty_cache()
@@ -284,6 +285,13 @@ def run_b200(args):
         def forward(x):
             with torch.no_grad():
                 h = sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols')
+                return F.log_softmax(h.float(), dim=1)
+
+        def forward_rows(x):
+            # the end-to-end entry: the rank's rows of x from the host; the first layout
+            # change (rows -> column slices, over NVLink) is part of the step
+            with torch.no_grad():
+                h = sliced_gcn_forward(graph, x, layers, relu=True, x_layout='rows')
                 return F.log_softmax(h.float(), dim=1)
 
     def barrier():
@@ -402,13 +410,14 @@ def run_b200(args):
     # ---- end to end: host buffers -> public API -> host result ----------------
     e2e = None
     if not args.no_e2e:
-        x_host = x_in.cpu().pin_memory()
+        x_e2e, fwd_e2e = (x_rows, forward_rows) if sliced else (x_in, forward)
+        x_host = x_e2e.cpu().pin_memory()
         out_host = torch.empty(out.shape, dtype=out.dtype).pin_memory()
-        x_stage = torch.empty_like(x_in)
+        x_stage = torch.empty_like(x_e2e)
 
         def e2e_step():
             x_stage.copy_(x_host, non_blocking=True)
-            o = forward(x_stage)
+            o = fwd_e2e(x_stage)
             out_host.copy_(o, non_blocking=True)
 
         for _ in range(2):
@@ -428,7 +437,7 @@ def run_b200(args):
         # still copies its own input from pinned memory and its own result back.
         cur = torch.cuda.current_stream()
         s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
-        x_stages = [x_stage, torch.empty_like(x_in)]
+        x_stages = [x_stage, torch.empty_like(x_e2e)]
         in_ready = [torch.cuda.Event() for _ in range(2)]
         in_free = [torch.cuda.Event() for _ in range(2)]
         outs = [None, None]
@@ -450,7 +459,7 @@ def run_b200(args):
                 cur.wait_event(in_ready[b])
                 if i >= 2:
                     cur.wait_event(out_done[b])          # result buffer of step i-2 was copied out
-                o = forward(x_stages[b])
+                o = fwd_e2e(x_stages[b])
                 in_free[b].record(cur)
                 outs[b] = o
                 ev = torch.cuda.Event()
