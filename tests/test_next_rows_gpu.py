@@ -1,0 +1,161 @@
+"""SURVEY §8(f) rows 2–3 on the GPU: the convolutions that fall onto the fused
+propagate routes (ChebConv, GraphConv, SGConv, APPNP, SAGEConv, GINConv, AGNNConv)
+and global pooling, against their unfused CPU restatement (oracle/ref_next.py):
+forward within 1e-5, gradients within 1e-4, max-pool bit-exact."""
+import pytest
+import torch
+
+from oracle import ref_next as R
+from util import assert_close, random_graph, skewed_graph
+
+pytestmark = pytest.mark.gpu
+
+
+def _graph(n, E, seed):
+    ei = random_graph(n, n, E, seed)                 # self-loops and duplicates included
+    ei[:, :5] = ei[:, 5:10]
+    return ei
+
+
+def _copy_params(dst, src):
+    sd = {k: v.detach().cpu().clone() for k, v in src.state_dict().items()}
+    missing = dst.load_state_dict(sd, strict=False)
+    assert not missing.unexpected_keys, missing
+
+
+def _check(gpu_mod, ref_mod, inputs_gpu, inputs_ref, fwd_tol=1e-5, grad_tol=1e-4):
+    xg = inputs_gpu[0].clone().requires_grad_(True)
+    xr = inputs_ref[0].clone().requires_grad_(True)
+    out = gpu_mod(xg, *inputs_gpu[1:])
+    ref = ref_mod(xr, *inputs_ref[1:])
+    assert_close(out, ref, fwd_tol, 'forward')
+    g = torch.randn(ref.shape, generator=torch.Generator().manual_seed(9))
+    out.backward(g.to(out.device))
+    ref.backward(g)
+    assert_close(xg.grad, xr.grad, grad_tol, 'grad x')
+    ref_params = dict(ref_mod.named_parameters())
+    for name, p in gpu_mod.named_parameters():
+        if name in ref_params and ref_params[name].grad is not None:
+            assert_close(p.grad, ref_params[name].grad, grad_tol, 'grad ' + name)
+
+
+@pytest.mark.parametrize('K', [1, 2, 4])
+@pytest.mark.parametrize('weighted', [False, True])
+def test_cheb_conv(dev, K, weighted):
+    from torch_geometric.nn import ChebConv
+    n, E, fin, fout = 300, 3000, 20, 12
+    ei = _graph(n, E, K)
+    x = torch.randn(n, fin, generator=torch.Generator().manual_seed(1))
+    w = torch.rand(E, generator=torch.Generator().manual_seed(2)) + 0.1 if weighted else None
+    torch.manual_seed(0)
+    m = ChebConv(fin, fout, K).to(dev)
+    r = R.ChebConv(fin, fout, K)
+    _copy_params(r, m)
+    extra_g = (ei.to(dev),) + ((w.to(dev),) if weighted else ())
+    extra_r = (ei,) + ((w,) if weighted else ())
+    _check(m, r, (x.to(dev),) + extra_g, (x,) + extra_r)
+
+
+@pytest.mark.parametrize('aggr', ['add', 'mean'])
+def test_graph_conv(dev, aggr):
+    from torch_geometric.nn import GraphConv
+    n, E, fin, fout = 250, 2500, 16, 24
+    ei = _graph(n, E, 3)
+    x = torch.randn(n, fin, generator=torch.Generator().manual_seed(1))
+    torch.manual_seed(0)
+    m = GraphConv(fin, fout, aggr=aggr).to(dev)
+    r = R.GraphConv(fin, fout, aggr=aggr)
+    _copy_params(r, m)
+    _check(m, r, (x.to(dev), ei.to(dev)), (x, ei))
+    if aggr == 'add':
+        w = torch.rand(E, generator=torch.Generator().manual_seed(2))
+        _check(m, r, (x.to(dev), ei.to(dev), w.to(dev)), (x, ei, w))
+
+
+@pytest.mark.parametrize('K', [1, 3])
+def test_sg_conv_and_appnp(dev, K):
+    from torch_geometric.nn import SGConv, APPNP
+    n, E, fin, fout = 400, 5000, 32, 7
+    ei = skewed_graph(n, E, 4)
+    x = torch.randn(n, fin, generator=torch.Generator().manual_seed(1))
+    torch.manual_seed(0)
+    m = SGConv(fin, fout, K=K).to(dev)
+    r = R.SGConv(fin, fout, K=K)
+    _copy_params(r, m)
+    _check(m, r, (x.to(dev), ei.to(dev)), (x, ei))
+    _check(APPNP(K, 0.1).to(dev), R.APPNP(K, 0.1), (x.to(dev), ei.to(dev)), (x, ei))
+
+
+def test_sg_conv_cached(dev):
+    from torch_geometric.nn import SGConv
+    n, E = 200, 1500
+    ei = _graph(n, E, 6).to(dev)
+    x = torch.randn(n, 8, generator=torch.Generator().manual_seed(1)).to(dev)
+    m = SGConv(8, 4, K=2, cached=True).to(dev)
+    a = m(x, ei)
+    b = m(x * 0 + 1, ei)                                # cached propagation is reused
+    assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize('normalize', [False, True])
+def test_sage_conv(dev, normalize):
+    from torch_geometric.nn import SAGEConv
+    n, E, fin, fout = 300, 2000, 12, 20
+    ei = _graph(n, E, 7)
+    x = torch.randn(n, fin, generator=torch.Generator().manual_seed(1))
+    torch.manual_seed(0)
+    m = SAGEConv(fin, fout, normalize=normalize).to(dev)
+    r = R.SAGEConv(fin, fout, normalize=normalize)
+    _copy_params(r, m)
+    _check(m, r, (x.to(dev), ei.to(dev)), (x, ei))
+
+
+def test_gin_conv(dev):
+    from torch_geometric.nn import GINConv
+    n, E, fin = 300, 2500, 10
+    ei = _graph(n, E, 8)
+    x = torch.randn(n, fin, generator=torch.Generator().manual_seed(1))
+    torch.manual_seed(0)
+    mlp = torch.nn.Sequential(torch.nn.Linear(fin, 16), torch.nn.ReLU(), torch.nn.Linear(16, 6))
+    mlp_r = torch.nn.Sequential(torch.nn.Linear(fin, 16), torch.nn.ReLU(), torch.nn.Linear(16, 6))
+    m = GINConv(mlp, eps=0.3)                           # re-initialises mlp (reset_parameters)
+    mlp_r.load_state_dict(m.nn.state_dict())
+    m = m.to(dev)
+    r = R.GINConv(mlp_r, eps=0.3)
+    _check(m, r, (x.to(dev), ei.to(dev)), (x, ei))
+
+
+def test_agnn_conv(dev):
+    from torch_geometric.nn import AGNNConv
+    n, E, fin = 300, 4000, 16
+    ei = skewed_graph(n, E, 9)
+    x = torch.randn(n, fin, generator=torch.Generator().manual_seed(1))
+    m = AGNNConv(requires_grad=True).to(dev)
+    m.beta.data.fill_(1.7)
+    r = R.AGNNConv(beta=1.7)
+    _check(m, r, (x.to(dev), ei.to(dev)), (x, ei), fwd_tol=2e-5)
+
+
+def test_global_pools(dev):
+    from torch_geometric.nn import global_add_pool, global_mean_pool, global_max_pool
+    g = torch.Generator().manual_seed(3)
+    sizes = [1, 40, 7, 300, 2, 90]
+    batch = torch.cat([torch.full((s,), i, dtype=torch.long) for i, s in enumerate(sizes)])
+    x = (torch.randint(-4, 5, (batch.numel(), 33), generator=g).float() / 4)     # ties for max
+    for fn, rf, exact in ((global_add_pool, R.global_add_pool, False),
+                          (global_mean_pool, R.global_mean_pool, False),
+                          (global_max_pool, R.global_max_pool, True)):
+        xg = x.to(dev).requires_grad_(True)
+        xr = x.clone().requires_grad_(True)
+        out, ref = fn(xg, batch.to(dev)), rf(xr, batch)
+        if exact:
+            assert torch.equal(out.cpu(), ref)
+        else:
+            assert_close(out, ref, 1e-6, fn.__name__)
+        w = torch.randn(ref.shape, generator=g)
+        (out * w.to(dev)).sum().backward()
+        (ref * w).sum().backward()
+        assert_close(xg.grad, xr.grad, 1e-6, fn.__name__ + ' grad')   # max: first maximum gets it
+    # explicit size with trailing empty graphs
+    out = global_add_pool(x.to(dev), batch.to(dev), size=9)
+    assert out.shape == (9, 33) and float(out[6:].abs().max()) == 0.0
