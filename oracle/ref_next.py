@@ -223,3 +223,23 @@ def knn_graph(x, k, batch=None, loop=False):
         src += [cand[t] for t in order]
         dst += [i] * len(order)
     return torch.tensor([src, dst], dtype=torch.long)
+
+
+# ---- TopKPooling (ConvexPruning.py:301-338): per-graph top-k by projection score --------
+def topk_pooling(x, edge_index, batch, weight, ratio):
+    """score = tanh(x.w / ||w||); per graph keep the ceil(ratio * n) best nodes (descending
+    score, graphs in order); x' = x[perm] * score[perm]; edges of the induced subgraph,
+    renumbered.  Plain Python loops.  Returns (x', edge_index', batch', perm, score[perm])."""
+    score = torch.tanh((x * weight.view(1, -1)).sum(-1) / weight.norm(p=2))
+    perm = []
+    for g in range(int(batch.max()) + 1):
+        ids = [i for i in range(x.size(0)) if int(batch[i]) == g]
+        k = -(-int(round(ratio * len(ids) * 1e6)) // 10 ** 6)          # ceil, float-safe
+        ids.sort(key=lambda i: (-float(score[i].detach()), i))
+        perm += ids[:k]
+    perm = torch.tensor(perm, dtype=torch.long)
+    pos = {int(v): i for i, v in enumerate(perm.tolist())}
+    keep = [(pos[int(a)], pos[int(b)]) for a, b in edge_index.t().tolist()
+            if int(a) in pos and int(b) in pos]
+    ei = torch.tensor(keep, dtype=torch.long).t().reshape(2, -1)
+    return x[perm] * score[perm].view(-1, 1), ei, batch[perm], perm, score[perm]

@@ -4,10 +4,10 @@ from .gat_conv import GATConv
 from .edge_conv import EdgeConv, DynamicEdgeConv
 from .simple_convs import ChebConv, GraphConv, SGConv, SAGEConv, AGNNConv, GINConv, APPNP
 from ._unported import (SplineConv, ARMAConv, RGCNConv, NNConv, GMMConv, PointConv, DNAConv,
-                        TopKPooling, SAGPooling)
+                        SAGPooling)
 
 __all__ = [
     'MessagePassing', 'GCNConv', 'GATConv', 'EdgeConv', 'DynamicEdgeConv', 'ChebConv',
     'GraphConv', 'SGConv', 'SAGEConv', 'AGNNConv', 'GINConv', 'APPNP', 'SplineConv', 'ARMAConv',
-    'RGCNConv', 'NNConv', 'GMMConv', 'PointConv', 'DNAConv', 'TopKPooling', 'SAGPooling',
+    'RGCNConv', 'NNConv', 'GMMConv', 'PointConv', 'DNAConv', 'SAGPooling',
 ]

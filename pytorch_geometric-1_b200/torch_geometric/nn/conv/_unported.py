@@ -23,5 +23,4 @@ NNConv = _unported('NNConv')
 GMMConv = _unported('GMMConv')
 PointConv = _unported('PointConv')
 DNAConv = _unported('DNAConv')
-TopKPooling = _unported('TopKPooling')
 SAGPooling = _unported('SAGPooling')

@@ -159,3 +159,38 @@ def test_global_pools(dev):
     # explicit size with trailing empty graphs
     out = global_add_pool(x.to(dev), batch.to(dev), size=9)
     assert out.shape == (9, 33) and float(out[6:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize('ratio', [0.8, 0.5, 0.34])
+def test_topk_pooling(dev, ratio):
+    """TopKPooling as the fork's topk_pool_Net calls it (ConvexPruning.py:306-327)."""
+    from torch_geometric.nn import TopKPooling, global_max_pool, global_mean_pool
+    g = torch.Generator().manual_seed(int(ratio * 100))
+    sizes = [13, 1, 40, 7, 25]
+    batch = torch.cat([torch.full((s,), i, dtype=torch.long) for i, s in enumerate(sizes)])
+    n = batch.numel()
+    x = torch.randn(n, 12, generator=g)
+    cum = [0]
+    for s_ in sizes:
+        cum.append(cum[-1] + s_)
+    ei = torch.cat([random_graph(s_, s_, 4 * s_, 10 + i) + cum[i] for i, s_ in enumerate(sizes)], 1)
+    torch.manual_seed(0)
+    pool = TopKPooling(12, ratio=ratio).to(dev)
+    xg = x.to(dev).requires_grad_(True)
+    xo, eio, _, bo, perm, score = pool(xg, ei.to(dev), None, batch.to(dev))
+    xr = x.clone().requires_grad_(True)
+    w = pool.weight.detach().cpu().view(-1).clone().requires_grad_(True)
+    rx, rei, rb, rperm, rscore = R.topk_pooling(xr, ei, batch, w, ratio)
+    assert torch.equal(perm.cpu(), rperm) and torch.equal(bo.cpu(), rb)
+    assert torch.equal(eio.cpu(), rei)
+    assert_close(xo, rx, 1e-6, 'pooled x')
+    assert_close(score, rscore, 1e-6, 'score')
+    # readout of the fork's model: cat(global max pool, global mean pool), gradients
+    ro = torch.cat([global_max_pool(xo, bo), global_mean_pool(xo, bo)], dim=1)
+    rr = torch.cat([R.global_max_pool(rx, rb), R.global_mean_pool(rx, rb)], dim=1)
+    assert_close(ro, rr, 1e-6, 'readout')
+    gw = torch.randn(rr.shape, generator=g)
+    (ro * gw.to(dev)).sum().backward()
+    (rr * gw).sum().backward()
+    assert_close(xg.grad, xr.grad, 1e-5, 'grad x')
+    assert_close(pool.weight.grad.view(-1), w.grad, 1e-5, 'grad weight')
