@@ -56,6 +56,8 @@ def parse():
                     help='N>1 layout: feature-sliced aggregation with peer-memory stores '
                          '(default) or all-to-all, or the destination-row partition with an '
                          'all-gather halo')
+    ap.add_argument('--fence', default='flags', choices=['flags', 'nccl'],
+                    help='sliced layout: rank barrier after a kernel that stored into peer memory')
     ap.add_argument('--row-groups', type=int, default=0,
                     help='sliced layout: number of row groups (0 = 2 on 8 GPUs, else 1)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -273,7 +275,8 @@ def run_b200(args):
         peer = args.dist == 'sliced' and dtype == torch.float32
         row_groups = args.row_groups or (2 if world >= 8 else 1)
         graph = SlicedGraph(ei_full, norm_full, n, rank, world,
-                            transport='peer' if peer else 'collective', row_groups=row_groups)
+                            transport='peer' if peer else 'collective', row_groups=row_groups,
+                            fence_mode=args.fence)
         del ei_full, norm_full
         x_in = graph.slice_cols(x_dev)                  # this rank's columns of all rows
         x_rows = graph.local_rows(x_dev).contiguous()   # e2e: every rank uploads its rows only
@@ -338,8 +341,10 @@ def run_b200(args):
         halo = {'layout': 'feature-sliced: whole graph on every rank, aggregation over the '
                           "rank's F/P columns of all rows, transform over the rank's rows",
                 'transport': 'plain stores into CUDA-IPC peer memory from the aggregation kernel '
-                             'and the column-scatter kernel; ranks meet at one-element NCCL '
-                             'all-reduces' if tr.fused else 'NCCL all_to_all_single',
+                             'and the GEMM epilogue; ranks meet at %s' %
+                             ('a one-block flag barrier over peer memory (pygb_peer_barrier)'
+                              if args.fence == 'flags' else 'one-element NCCL all-reduces')
+                             if tr.fused else 'NCCL all_to_all_single',
                 'bytes_sent_per_gpu_per_step': h_bytes,
                 'collectives_per_step': (tr.collectives - coll0) / args.steps,
                 'ms_per_step': (sum(a.elapsed_time(b) for a, b, _ in hl) / args.steps

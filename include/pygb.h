@@ -335,6 +335,16 @@ int pygb_peer_export(const void* ptr, void* handle, size_t handle_bytes);
 int pygb_peer_open(const void* handle, size_t handle_bytes, void** ptr);
 int pygb_peer_close(void* ptr);
 
+/* Barrier of the ranks of one box over peer memory (one process per GPU, every rank on its
+ * own device).  flag_tab: DEVICE array of `world` pointers, entry q = the block of `world`
+ * zero-initialised 64-bit flags that lives in rank q's arena (as mapped in this process).
+ * Every rank calls it with the same, strictly increasing `epoch` (1, 2, ...).  Kernels launched
+ * on the stream before the call have completed — their stores into peer memory included —
+ * before any rank's kernels after the call start.  A rank that waits longer than timeout_ns
+ * traps.  Replaces a one-element NCCL all-reduce (≈4x lower latency). */
+int pygb_peer_barrier(void* const* flag_tab, int32_t rank, int32_t world, int64_t epoch,
+                      int64_t timeout_ns, pygb_stream_t s);
+
 /* Row layout -> column layout: src is this rank's rows [n_rows, n_parts*Fc]
  * (row stride lds); column block q goes to
  *   (T*)dst_tab[q * n_dup + d] + (dst_row0 + r) * ldd + c,   c < Fc, d < n_dup,

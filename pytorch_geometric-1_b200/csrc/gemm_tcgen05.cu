@@ -17,11 +17,17 @@
 // Persistent CTAs (one per SM) of 10 warps: warp 0 TMA producer, warp 1 TMEM
 // allocator + MMA issuer (one elected lane), warps 2-5 splitter, warps 6-9 epilogue
 // (TMEM -> registers -> global).  Tile 128 x BN (BN = N rounded to 16, <= 256) x 32
-// (one 128-byte swizzle atom of fp32), 2-4 stages.  Barriers per stage: full (TMA
+// (one 128-byte swizzle atom of fp32), 2-6 stages.  Two other shapes are compiled and
+// bit-identical (tests/test_gemm_gpu.py): 128 x BN x 16 and 256 x BN x 16 (64-byte
+// swizzle atoms; the 256-row tile shares every W stage between two 128-row halves).
+// On the cfg5 shapes they are not faster (profiles/r01_k5_tiles.md): the kernel is paced
+// by the sum of small costs around the MMAs, not by the shared-memory fill.  Barriers per stage: full (TMA
 // bytes landed) -> ready (split done, 128 arrivals) -> empty (tcgen05.commit after
 // the MMAs read the stage).  Two accumulator buffers in TMEM (acc_full / acc_empty)
 // let the epilogue of tile t run under the main loop of tile t+1.
 #include <cuda.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #include <mutex>
 
@@ -33,6 +39,7 @@ namespace {
 constexpr int kBM = 128;
 constexpr int kBK = 32;  // fp32 elements = 128 bytes = one swizzle atom
 constexpr int kGemmThreads = 320;
+constexpr int kMaxStages = 6;
 constexpr int kATileBytes = kBM * kBK * 4;  // 16 KB
 constexpr int kEpiRowFloats = 36;           // 32 columns + 4 pad: conflict-free 128-bit transposes
 constexpr int kEpiWarpBytes = 32 * kEpiRowFloats * 4;
@@ -145,6 +152,12 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
 
 constexpr int kMaxDup = 4;  // destinations per column block of the routed epilogue
 
+// K-major, 64-byte swizzle, rows of 64 bytes packed: 8-row groups 512 bytes apart.
+__device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t saddr) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (32ull << 32) | (1ull << 46) |
+         (4ull << 61);
+}
+
 struct GemmParams {
   const float* bias;
   int relu;  // max(x, 0) after the bias (NaN stays NaN, like torch.relu)
@@ -153,8 +166,9 @@ struct GemmParams {
   int M, N, K;
   int a_kw;       // columns per plane of A (K when A is one row-major matrix)
   int BN;         // N tile (multiple of 16, <= 256)
-  int stages;     // 2..4
-  int tmem_cols;  // power of two >= 2*BN (two accumulator buffers)
+  int stages;     // 2..kMaxStages
+  int tmem_cols;  // power of two >= acc_bufs * MH * BN
+  int acc_bufs;   // accumulator buffers in TMEM (2: the epilogue overlaps the next main loop)
   int m_tiles, n_tiles;
   // routed output (row layout -> column layout fused into the epilogue): column block
   // q = col / c_fc of row r goes to c_tab[q * c_dup + d] + (c_row0 + r) * c_ldd + col % c_fc
@@ -167,12 +181,21 @@ struct GemmParams {
 // PASSES = 3: 3xTF32 split (fp32-faithful);  PASSES = 1: plain TF32.
 // Persistent: CTA b works on tiles b, b+grid, ...  (n fastest, so the A tile of a
 // row block is re-read from L2 when N spans several tiles).
-template <int PASSES>
+// MH = 1: tile 128 x BN x 32 (128-byte swizzle atoms).  MH = 2: tile 256 x BN x 16 (64-byte
+// swizzle atoms): the two 128-row halves share every W tile, so a k-step of 32 moves
+// 2*16 + 2*BN*64*2/1024 KB for 256 rows instead of 16 + 2*BN*128/1024 KB for 128 — 40 % fewer
+// bytes from L2 per flop at BN = 256, where the shared-memory fill rate bounds the main loop.
+template <int PASSES, int MH, int BKT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBh,
                  const __grid_constant__ CUtensorMap mapBl, const GemmParams P) {
+  constexpr int kBK = BKT;                        // shadows the namespace constants
+  constexpr int kTileM = MH * kBM;
+  constexpr int kATileBytes = kTileM * kBK * 4;
+  constexpr bool SW64 = BKT == 16;                // 64-byte rows -> 64-byte swizzle atoms
+  static_assert(BKT == 16 || BKT == 32, "k-step of one 64- or 128-byte swizzle row");
   extern __shared__ __align__(1024) unsigned char gsm[];
-  __shared__ __align__(8) uint64_t bars[3 * 4 + 4];
+  __shared__ __align__(8) uint64_t bars[3 * kMaxStages + 4];
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int BN = P.BN, S = P.stages;
@@ -185,13 +208,15 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   auto b_lo = [&](int s) { return b_hi(s) + b_bytes; };
   const uint32_t bar0 = smem_u32(bars);
   auto full = [&](int s) { return bar0 + 8u * s; };
-  auto ready = [&](int s) { return bar0 + 8u * (4 + s); };
-  auto empty = [&](int s) { return bar0 + 8u * (8 + s); };
-  auto acc_full = [&](int b) { return bar0 + 8u * (12 + b); };
-  auto acc_empty = [&](int b) { return bar0 + 8u * (14 + b); };
+  auto ready = [&](int s) { return bar0 + 8u * (kMaxStages + s); };
+  auto empty = [&](int s) { return bar0 + 8u * (2 * kMaxStages + s); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (3 * kMaxStages + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (3 * kMaxStages + 2 + b); };
 
   const int nk = (P.K + kBK - 1) / kBK;
   const int n_tiles_total = P.m_tiles * P.n_tiles;
+  const int acc_cols = MH * BN;                   // TMEM columns of one accumulator buffer
+  const int nbuf = P.acc_bufs;                    // 2, or 1 when 2 * acc_cols > 512
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) {
@@ -225,7 +250,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       if (PASSES == 3) asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBl) : "memory");
       int it = 0;
       for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-        const int m0 = (tile / P.n_tiles) * kBM, n0 = (tile % P.n_tiles) * BN;
+        const int m0 = (tile / P.n_tiles) * kTileM, n0 = (tile % P.n_tiles) * BN;
         for (int kt = 0; kt < nk; ++kt, ++it) {
           const int s = it % S;
           const uint32_t ph = (uint32_t)(it / S) & 1u;
@@ -247,24 +272,31 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                              ((uint32_t)(kBM >> 4) << 24);
       int it = 0, tl = 0;
       for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++tl) {
-        const int buf = tl & 1;
-        mbar_wait(acc_empty(buf), ((uint32_t)(tl >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
+        const int buf = tl % nbuf;
+        mbar_wait(acc_empty(buf), ((uint32_t)(tl / nbuf) & 1u) ^ 1u);  // epilogue drained this buffer
         tcgen05_fence_after();
-        const uint32_t dcol = tmem_d + (uint32_t)(buf * BN);
+        const uint32_t dcol = tmem_d + (uint32_t)(buf * acc_cols);
         for (int kt = 0; kt < nk; ++kt, ++it) {
           const int s = it % S;
           const uint32_t ph = (uint32_t)(it / S) & 1u;
           mbar_wait(PASSES == 3 ? ready(s) : full(s), ph);
           tcgen05_fence_after();
-          const uint64_t dah = smem_desc_sw128(a_hi(s)), dbh = smem_desc_sw128(b_hi(s));
-          const uint64_t dal = smem_desc_sw128(a_lo(s)), dbl = smem_desc_sw128(b_lo(s));
+          const uint64_t dbh = SW64 ? smem_desc_sw64(b_hi(s)) : smem_desc_sw128(b_hi(s));
+          const uint64_t dbl = SW64 ? smem_desc_sw64(b_lo(s)) : smem_desc_sw128(b_lo(s));
 #pragma unroll
-          for (int k = 0; k < kBK / 8; ++k) {  // UMMA_K = 8 tf32 = 32 bytes -> +2 in the address field
-            const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
-            mma_tf32(dcol, dah + 2u * k, dbh + 2u * k, idesc, acc);
-            if (PASSES == 3) {
-              mma_tf32(dcol, dal + 2u * k, dbh + 2u * k, idesc, 1u);
-              mma_tf32(dcol, dah + 2u * k, dbl + 2u * k, idesc, 1u);
+          for (int h = 0; h < MH; ++h) {       // 128-row halves of the tile share the W stage
+            const uint32_t hoff = (uint32_t)(h * kBM * kBK * 4);
+            const uint64_t dah = SW64 ? smem_desc_sw64(a_hi(s) + hoff) : smem_desc_sw128(a_hi(s) + hoff);
+            const uint64_t dal = SW64 ? smem_desc_sw64(a_lo(s) + hoff) : smem_desc_sw128(a_lo(s) + hoff);
+            const uint32_t dc = dcol + (uint32_t)(h * BN);
+#pragma unroll
+            for (int k = 0; k < kBK / 8; ++k) {  // UMMA_K = 8 tf32 = 32 bytes -> +2 in the address field
+              const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
+              mma_tf32(dc, dah + 2u * k, dbh + 2u * k, idesc, acc);
+              if (PASSES == 3) {
+                mma_tf32(dc, dal + 2u * k, dbh + 2u * k, idesc, 1u);
+                mma_tf32(dc, dah + 2u * k, dbl + 2u * k, idesc, 1u);
+              }
             }
           }
           tcgen05_commit(empty(s));  // frees the stage once the MMAs have read it
@@ -317,12 +349,13 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const int rr = lane >> 3, jj = lane & 7;
     int tl = 0;
     for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++tl) {
-      const int m0 = (tile / P.n_tiles) * kBM, n0 = (tile % P.n_tiles) * BN;
-      const int buf = tl & 1;
-      mbar_wait(acc_full(buf), (uint32_t)(tl >> 1) & 1u);
+      const int m0 = (tile / P.n_tiles) * kTileM, n0 = (tile % P.n_tiles) * BN;
+      const int buf = tl % nbuf;
+      mbar_wait(acc_full(buf), (uint32_t)(tl / nbuf) & 1u);
       tcgen05_fence_after();
-      const int row0 = m0 + q * 32;
-      const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BN);
+      for (int h = 0; h < MH; ++h) {
+      const int row0 = m0 + h * kBM + q * 32;
+      const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * acc_cols + h * BN);
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t r[32];
         if (c0 + 32 <= BN) {
@@ -386,6 +419,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         }
         __syncwarp();
       }
+      }
       tcgen05_fence_before();
       mbar_arrive(acc_empty(buf));  // 128 arrivals: the MMA warp may overwrite this buffer
     }
@@ -436,7 +470,7 @@ EncodeTiledFn encode_fn() {
 
 // 2-D fp32 row-major [rows, cols] with row stride ld (elements); box = [box_rows, 32 cols]
 int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld,
-             int box_rows) {
+             int box_rows, int bk) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -444,10 +478,11 @@ int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int
   }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
-  cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides,
-                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  bk == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) for [%lld x %lld] ld %lld", (int)r,
@@ -459,7 +494,7 @@ int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int
 
 // A as `slices` planes of [rows, cols] (row stride ld, plane stride `plane` elements).
 int make_map_a(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld,
-               int64_t slices, int64_t plane) {
+               int64_t slices, int64_t plane, int box_rows, int bk) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -467,10 +502,11 @@ int make_map_a(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, i
   }
   cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)slices};
   cuuint64_t strides[2] = {(cuuint64_t)ld * 4, (cuuint64_t)(slices > 1 ? plane : ld * rows) * 4};
-  cuuint32_t box[3] = {(cuuint32_t)kBK, (cuuint32_t)kBM, 1};
+  cuuint32_t box[3] = {(cuuint32_t)bk, (cuuint32_t)box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(ptr), dims, strides,
-                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  bk == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) for A [%lld x %lld x %lld] ld %lld", (int)r,
@@ -551,47 +587,69 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
   P.K = (int)K;
   P.a_kw = (int)a_kw;
   P.BN = Np < 256 ? Np : 256;
-  int tc = 32;
-  while (tc < 2 * P.BN) tc <<= 1;
-  P.tmem_cols = tc;  // two accumulator buffers of BN columns
-  P.m_tiles = (int)ceil_div(M, kBM);
   P.n_tiles = (int)ceil_div(Np, P.BN);
-  const size_t b_bytes = (size_t)P.BN * kBK * 4;
-  const size_t stage_bytes = (passes == 3 ? 2 : 1) * (kATileBytes + b_bytes);
-  const size_t budget = 226 * 1024;
-  int stages = (int)((budget - 1024 - kEpiBytes) / stage_bytes);
-  if (stages > 4) stages = 4;
-  const int nk = (int)ceil_div(K, kBK);
-  if (stages > nk) stages = nk < 2 ? 2 : nk;
-  PYGB_REQUIRE(stages >= 2, "pygb_gemm_xw: tile does not fit shared memory");
-  P.stages = stages;
-  const size_t smem = stages * stage_bytes + kEpiBytes + 1024;
-
-  CUtensorMap mapA, mapBh, mapBl;
-  int rc = make_map_a(&mapA, A, M, a_kw, lda, a_slices, a_plane);
-  if (rc) return rc;
-  rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN);
-  if (rc) return rc;
-  rc = make_map(&mapBl, Wl, Np, Kp, Kp, P.BN);
-  if (rc) return rc;
-
   int sms = 148;
   {
     int dev = 0;
     PYGB_CUDA(cudaGetDevice(&dev));
     PYGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   }
+  // Tile shape.  256 x BN x 16 shares every W stage between two 128-row halves: worth it when
+  // W traffic dominates the stage (3 passes, wide BN) and there are enough tiles for every SM.
+  int mh = 1, bk = kBK;
+  if (const char* e = getenv("PYGB_GEMM_TILE")) {     // tuning / tests: "128x32", "128x16", "256x16"
+    int tm = 0, tk = 0;
+    if (sscanf(e, "%dx%d", &tm, &tk) == 2 && (tm == 128 || tm == 256) && (tk == 16 || tk == 32) &&
+        !(tm == 256 && tk == 32)) {
+      mh = tm / 128;
+      bk = tk;
+    }
+  }
+  const int acc_cols = mh * P.BN;
+  P.acc_bufs = 2 * acc_cols <= 512 ? 2 : 1;
+  int tc = 32;
+  while (tc < P.acc_bufs * acc_cols) tc <<= 1;
+  P.tmem_cols = tc;
+  P.m_tiles = (int)ceil_div(M, mh * kBM);
+  const size_t b_bytes = (size_t)P.BN * bk * 4;
+  const size_t a_bytes = (size_t)mh * kBM * bk * 4;
+  const size_t stage_bytes = (passes == 3 ? 2 : 1) * (a_bytes + b_bytes);
+  const size_t budget = 226 * 1024;
+  int stages = (int)((budget - 1024 - kEpiBytes) / stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  const int nk = (int)ceil_div(K, bk);
+  if (stages > nk) stages = nk < 2 ? 2 : nk;
+  PYGB_REQUIRE(stages >= 2, "pygb_gemm_xw: tile does not fit shared memory");
+  P.stages = stages;
+  const size_t smem = stages * stage_bytes + kEpiBytes + 1024;
+
+  CUtensorMap mapA, mapBh, mapBl;
+  int rc = make_map_a(&mapA, A, M, a_kw, lda, a_slices, a_plane, mh * kBM, bk);
+  if (rc) return rc;
+  rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN, bk);
+  if (rc) return rc;
+  rc = make_map(&mapBl, Wl, Np, Kp, Kp, P.BN, bk);
+  if (rc) return rc;
+
   const int64_t tiles = (int64_t)P.m_tiles * P.n_tiles;
   dim3 grid((unsigned)(tiles < sms ? tiles : sms));
+#define PYGB_GEMM_LAUNCH(PS, MHV, BKV)                                                         \
+  do {                                                                                         \
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<PS, MHV, BKV>,                             \
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize,                \
+                                   (int)(226 * 1024)));                                        \
+    gemm_tf32_kernel<PS, MHV, BKV><<<grid, kGemmThreads, smem, st>>>(mapA, mapBh, mapBl, P);   \
+  } while (0)
   if (passes == 3) {
-    PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)(226 * 1024)));
-    gemm_tf32_kernel<3><<<grid, kGemmThreads, smem, st>>>(mapA, mapBh, mapBl, P);
+    if (mh == 2) PYGB_GEMM_LAUNCH(3, 2, 16);
+    else if (bk == 16) PYGB_GEMM_LAUNCH(3, 1, 16);
+    else PYGB_GEMM_LAUNCH(3, 1, 32);
   } else {
-    PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)(226 * 1024)));
-    gemm_tf32_kernel<1><<<grid, kGemmThreads, smem, st>>>(mapA, mapBh, mapBl, P);
+    if (mh == 2) PYGB_GEMM_LAUNCH(1, 2, 16);
+    else if (bk == 16) PYGB_GEMM_LAUNCH(1, 1, 16);
+    else PYGB_GEMM_LAUNCH(1, 1, 32);
   }
+#undef PYGB_GEMM_LAUNCH
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }

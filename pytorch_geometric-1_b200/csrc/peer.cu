@@ -51,6 +51,39 @@ cols_scatter_kernel(const T* __restrict__ src, int64_t lds, int64_t n_rows, int 
   }
 }
 
+// One-block barrier over peer memory.  Rank r holds a block of `world` 64-bit flags; thread q
+// of rank r stores `epoch` (release, system scope) into flag r of rank q, then waits until flag
+// q of its own block reaches `epoch` (acquire, system scope).  Epochs only grow, so a flag
+// never has to be reset.  The kernels launched before the barrier on this stream have
+// completed, hence their stores into peer memory precede the flag store; the kernels launched
+// after it start only once every rank has arrived.  A rank that waits longer than timeout_ns
+// traps (the process fails loudly instead of hanging the GPU).
+__global__ void peer_barrier_kernel(unsigned long long* const* __restrict__ flag_tab, int rank,
+                                    int world, unsigned long long epoch,
+                                    unsigned long long timeout_ns) {
+  const int q = threadIdx.x;
+  if (q < world) {
+    __threadfence_system();
+    unsigned long long* remote = flag_tab[q] + rank;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(remote), "l"(epoch) : "memory");
+    const unsigned long long* mine = flag_tab[rank] + q;
+    unsigned long long t0, t1, v;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
+      if (v >= epoch) break;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+      if (t1 - t0 > timeout_ns) {
+        printf("pygb_peer_barrier: rank %d waited %llu ns for rank %d (epoch %llu, saw %llu)\n",
+               rank, timeout_ns, q, epoch, v);
+        __trap();
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+}
+
 }  // namespace
 }  // namespace pygb
 
@@ -90,6 +123,18 @@ int pygb_peer_open(const void* handle, size_t handle_bytes, void** ptr) {
 
 int pygb_peer_close(void* ptr) {
   if (ptr) PYGB_CUDA(cudaIpcCloseMemHandle(ptr));
+  return PYGB_OK;
+}
+
+int pygb_peer_barrier(void* const* flag_tab, int32_t rank, int32_t world, int64_t epoch,
+                      int64_t timeout_ns, pygb_stream_t s) {
+  PYGB_REQUIRE(flag_tab && world >= 1 && world <= 64 && rank >= 0 && rank < world && epoch > 0 &&
+                   timeout_ns > 0,
+               "pygb_peer_barrier: bad arguments (world <= 64, epoch > 0)");
+  peer_barrier_kernel<<<1, 64, 0, as_stream(s)>>>(
+      reinterpret_cast<unsigned long long* const*>(flag_tab), rank, world,
+      (unsigned long long)epoch, (unsigned long long)timeout_ns);
+  PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }
 

@@ -49,6 +49,7 @@ SIGNATURES = {
     'pygb_peer_export': (_I, [_P, _P, _Z]),
     'pygb_peer_open': (_I, [_P, _Z, _P]),
     'pygb_peer_close': (_I, [_P]),
+    'pygb_peer_barrier': (_I, [_P, _I, _I, _L, _L, _P]),
     'pygb_cols_scatter': (_I, [_I, _P, _L, _L, _L, _I, _I, _P, _L, _L, _I, _P]),
     'pygb_gemm_xw_routed': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _L, _L, _I,
                                  _P, _Z, _P]),

@@ -211,9 +211,12 @@ class PeerTransport(object):
     """Layout changes by plain stores into peer HBM (CUDA IPC over NVLink)."""
 
     fused = True
+    _FLAG_BYTES = 1024                  # 64 ranks x 8-byte epoch flags at the head of the arena
+    FENCE_TIMEOUT_NS = 20 * 10 ** 9
 
-    def __init__(self, plan, device, group=None):
+    def __init__(self, plan, device, group=None, fence_mode='flags'):
         from .. import _native as nat
+        self.fence_mode = fence_mode
         self.nat = nat
         self.plan, self.group, self.device = plan, group, torch.device(device)
         if plan.Gr > 4:
@@ -251,7 +254,7 @@ class PeerTransport(object):
         nat, p = self.nat, self.plan
         self.close()
         r_bytes, c_bytes = self._layout(fp_max)
-        total = 2 * r_bytes + c_bytes
+        total = self._FLAG_BYTES + 2 * r_bytes + c_bytes
         with torch.cuda.device(self.device):
             base = ctypes.c_void_p()
             nat.call_host('pygb_peer_alloc', ctypes.c_size_t(total), ctypes.byref(base))
@@ -275,8 +278,10 @@ class PeerTransport(object):
                 self._peer.append(int(ptr.value))
                 self._opened.append(int(ptr.value))
         self._base, self._cap = int(base.value), fp_max
-        self._r_off = (0, r_bytes)
-        self._c_off = 2 * r_bytes
+        self._r_off = (self._FLAG_BYTES, self._FLAG_BYTES + r_bytes)
+        self._c_off = self._FLAG_BYTES + 2 * r_bytes
+        self._flag_tab = torch.tensor(self._peer, dtype=torch.int64).to(self.device)
+        self._epoch = 0
         self._mem = torch.as_tensor(_DevMem(self._base, total), device=self.device)
         self._tabs = {}
         self.fence()
@@ -307,9 +312,17 @@ class PeerTransport(object):
 
     def fence(self):
         """All ranks' earlier kernels (and their peer stores) are complete before any
-        rank's later kernels start: a one-element all-reduce on the current stream."""
-        if self.plan.world_size > 1:
-            dist.all_reduce(self._flag, group=self.group)
+        rank's later kernels start.  ``fence_mode='flags'``: a one-block kernel that
+        exchanges epoch flags through the peer-mapped arenas (pygb_peer_barrier);
+        ``'nccl'``: a one-element all-reduce on the current stream."""
+        p = self.plan
+        if p.world_size > 1:
+            if self.fence_mode == 'flags' and self._base is not None:
+                self._epoch += 1
+                self.nat.call('pygb_peer_barrier', self.device, self.nat.ptr(self._flag_tab),
+                              p.rank, p.world_size, self._epoch, self.FENCE_TIMEOUT_NS)
+            else:
+                dist.all_reduce(self._flag, group=self.group)
         self.collectives += 1
 
     def _check(self, t):
@@ -422,7 +435,7 @@ class SlicedGraph(object):
     graph when there is one row group — plus the row block / column slice bookkeeping."""
 
     def __init__(self, edge_index, norm, num_nodes, rank, world_size, group=None, i=1,
-                 transport='peer', build_adj=True, row_groups=1):
+                 transport='peer', build_adj=True, row_groups=1, fence_mode='flags'):
         self.plan = p = SlicePlan(num_nodes, world_size, rank, row_groups)
         self.i = i
         self.device = edge_index.device
@@ -442,7 +455,7 @@ class SlicedGraph(object):
             self.adj = Adj(edge_index, i, size)
             self.w_csr = None if norm is None else self.adj.permuted(norm.float(), 'dst')
         if transport == 'peer':
-            self.transport = PeerTransport(p, self.device, group)
+            self.transport = PeerTransport(p, self.device, group, fence_mode)
         elif transport == 'collective':
             self.transport = CollectiveTransport(p, group)
         else:

@@ -89,7 +89,7 @@ def test_dist_gcn_two_gpus_nccl():
 
 
 # ---- feature-sliced layout ---------------------------------------------------------
-def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups):
+def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence='flags'):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for p in (root, os.path.join(root, 'pytorch_geometric-1_b200'), os.path.join(root, 'tests')):
@@ -112,7 +112,8 @@ def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups):
         dims = [(100, 256), (256, 256), (256, 47)]
         layers = [(torch.randn(a, b) / a ** 0.5, torch.randn(b)) for a, b in dims]
         ei2, norm = GCNConv.norm(ei.to(dev), n, None, False, torch.float32)
-        g = SlicedGraph(ei2, norm, n, rank, world, transport=transport, row_groups=row_groups)
+        g = SlicedGraph(ei2, norm, n, rank, world, transport=transport, row_groups=row_groups,
+                        fence_mode=fence)
         pl = g.plan
         xin = g.slice_cols(x.to(dev)) if x_layout == 'cols' else g.local_rows(x.to(dev)).contiguous()
         lay = [(w.to(dev), b.to(dev)) for w, b in layers]
@@ -140,11 +141,11 @@ def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups):
         dist.destroy_process_group()
 
 
-def _run_sliced(world, transport, x_layout, row_groups=1):
+def _run_sliced(world, transport, x_layout, row_groups=1, fence='flags'):
     ctx = mp.get_context('spawn')
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, transport, x_layout, row_groups))
+    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, transport, x_layout, row_groups, fence))
              for r in range(world)]
     for p in procs:
         p.start()
@@ -162,6 +163,12 @@ def test_sliced_gcn_two_gpus(transport, x_layout, row_groups):
     if torch.cuda.device_count() < 2:
         pytest.skip('needs two GPUs')
     _run_sliced(2, transport, x_layout, row_groups)
+
+
+def test_sliced_gcn_two_gpus_nccl_fence():
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs')
+    _run_sliced(2, 'peer', 'cols', 1, fence='nccl')
 
 
 @pytest.mark.parametrize('transport', ['collective', 'peer'])

@@ -64,6 +64,46 @@ def test_gemm_slice_major_operand(dev, M, S, Kc, N):
     assert got.shape == (M, N) and torch.equal(got, ref)
 
 
+@pytest.mark.parametrize('M,K,N', [(1000, 100, 256), (777, 256, 256), (300, 256, 47),
+                                   (130, 500, 512), (4097, 64, 128), (1, 8, 3), (257, 16, 16)])
+def test_gemm_tile_shapes_agree(dev, monkeypatch, M, K, N):
+    """The 256-row tile (two halves sharing each W stage, 64-byte swizzle, k-step 16) gives
+    the same bits as the 128-row tile: same products, same accumulation order per element."""
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(M + K + N)
+    x = torch.randn(M, K, generator=g).to(dev)
+    w = (torch.randn(K, N, generator=g) / K ** 0.5).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    monkeypatch.setenv('PYGB_GEMM_TILE', '128x32')
+    ref = ops.gemm_xw_raw(x, w, b, relu=True)
+    ref1 = ops.gemm_xw_raw(x, w, None, passes=1)
+    for tile in ('256x16', '128x16'):
+        monkeypatch.setenv('PYGB_GEMM_TILE', tile)
+        got = ops.gemm_xw_raw(x, w, b, relu=True)
+        got1 = ops.gemm_xw_raw(x, w, None, passes=1)
+        assert torch.equal(got, ref) and torch.equal(got1, ref1), tile
+    assert _rel(ops.gemm_xw_raw(x, w, b), x.double().cpu() @ w.double().cpu() + b.double().cpu()) <= 1e-5
+
+
+def test_gemm_tile_256_sliced_and_routed(dev, monkeypatch):
+    from torch_geometric import ops
+    monkeypatch.setenv('PYGB_GEMM_TILE', '256x16')
+    g = torch.Generator().manual_seed(5)
+    M, S, Kc, N, Fc = 900, 4, 32, 256, 64
+    x = torch.randn(M, S * Kc, generator=g).to(dev)
+    w = (torch.randn(S * Kc, N, generator=g) / (S * Kc) ** 0.5).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    ref = ops.gemm_xw_raw(x, w, b, relu=True)
+    planes = torch.zeros((S, M + 11, Kc), device=dev)
+    planes[:, :M] = x.view(M, S, Kc).permute(1, 0, 2)
+    assert torch.equal(ops.gemm_xw_raw(planes, w, b, relu=True, rows=M), ref)
+    outs = [torch.full((M + 2, Fc), -7.0, device=dev) for _ in range(N // Fc)]
+    tab = torch.tensor([o.data_ptr() for o in outs], dtype=torch.int64).to(dev)
+    ops.gemm_xw_routed_raw(x, w, b, Fc, tab, 2, Fc, relu=True)
+    for q, o in enumerate(outs):
+        assert torch.equal(o[2:], ref[:, q * Fc:(q + 1) * Fc]) and float(o[:2].max()) == -7.0
+
+
 @pytest.mark.parametrize('M,K,N', SHAPES[:5])
 def test_gemm_tf32_single_pass(dev, M, K, N):
     from torch_geometric import ops
