@@ -56,7 +56,7 @@ def parse():
                     help='N>1 layout: feature-sliced aggregation with peer-memory stores '
                          '(default) or all-to-all, or the destination-row partition with an '
                          'all-gather halo')
-    ap.add_argument('--fence', default='flags', choices=['flags', 'nccl'],
+    ap.add_argument('--fence', default='nccl', choices=['flags', 'nccl'],
                     help='sliced layout: rank barrier after a kernel that stored into peer memory')
     ap.add_argument('--row-groups', type=int, default=0,
                     help='sliced layout: number of row groups (0 = 2 on 8 GPUs, else 1)')

@@ -165,6 +165,7 @@ struct GemmParams {
   int64_t ldc;
   int M, N, K;
   int a_kw;       // columns per plane of A (K when A is one row-major matrix)
+  int a_3d;       // A is several planes: 3-D tensor map
   int BN;         // N tile (multiple of 16, <= 256)
   int stages;     // 2..kMaxStages
   int tmem_cols;  // power of two >= acc_bufs * MH * BN
@@ -257,8 +258,13 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           mbar_wait(empty(s), ph ^ 1u);
           mbar_expect_tx(full(s), kATileBytes + (PASSES == 3 ? 2 : 1) * b_bytes);
           {  // A is a_slices planes of [M, a_kw] columns (one plane: ordinary row-major)
-            const int kcol = kt * kBK, sl = kcol / P.a_kw;
-            tma_load_3d(a_hi(s), &mapA, full(s), kcol - sl * P.a_kw, m0, sl);
+            const int kcol = kt * kBK;
+            if (P.a_3d) {
+              const int sl = kcol / P.a_kw;
+              tma_load_3d(a_hi(s), &mapA, full(s), kcol - sl * P.a_kw, m0, sl);
+            } else {
+              tma_load_2d(a_hi(s), &mapA, full(s), kcol, m0);
+            }
           }
           tma_load_2d(b_hi(s), &mapBh, full(s), kt * kBK, n0);
           if (PASSES == 3) tma_load_2d(b_lo(s), &mapBl, full(s), kt * kBK, n0);
@@ -381,39 +387,53 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           if (col + 2 < P.N) bv.z = __ldg(P.bias + col + 2);
           if (col + 3 < P.N) bv.w = __ldg(P.bias + col + 3);
         }
-        float* route_base[kMaxDup];
-        if (P.c_tab != nullptr && col < P.N) {
-          const int qb = col / P.c_fc;
-          for (int d = 0; d < P.c_dup; ++d)
-            route_base[d] = P.c_tab[qb * P.c_dup + d] + P.c_row0 * P.c_ldd + (col - qb * P.c_fc);
-        }
+        const bool col_ok = col < P.N;
+        if (P.c_tab == nullptr) {       // plain C: the hot path stays branch-free inside the row loop
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rl = i * 4 + rr;
-          float4 v;
-          asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
-                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                       : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
-          v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
-          if (P.relu) {
-            v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
-            v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
-          }
-          const int row = row0 + rl;
-          if (row < P.M && col < P.N) {
-            if (P.c_tab != nullptr) {   // N and c_fc are multiples of 4 here: whole vectors
-              for (int d = 0; d < P.c_dup; ++d)
-                *reinterpret_cast<float4*>(route_base[d] + (int64_t)row * P.c_ldd) = v;
-              continue;
+          for (int i = 0; i < 8; ++i) {
+            const int rl = i * 4 + rr;
+            float4 v;
+            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                         : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
+            v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+            if (P.relu) {
+              v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
+              v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
             }
-            float* dst = P.C + (int64_t)row * P.ldc + col;
-            if (vec_ok && col + 4 <= P.N) {
-              *reinterpret_cast<float4*>(dst) = v;
-            } else {
-              dst[0] = v.x;
-              if (col + 1 < P.N) dst[1] = v.y;
-              if (col + 2 < P.N) dst[2] = v.z;
-              if (col + 3 < P.N) dst[3] = v.w;
+            const int row = row0 + rl;
+            if (row < P.M && col_ok) {
+              float* dst = P.C + (int64_t)row * P.ldc + col;
+              if (vec_ok && col + 4 <= P.N) {
+                *reinterpret_cast<float4*>(dst) = v;
+              } else {
+                dst[0] = v.x;
+                if (col + 1 < P.N) dst[1] = v.y;
+                if (col + 2 < P.N) dst[2] = v.z;
+                if (col + 3 < P.N) dst[3] = v.w;
+              }
+            }
+          }
+        } else {                        // routed: N and c_fc are multiples of 4 -> whole vectors
+          const int qb = col_ok ? col / P.c_fc : 0;
+          const int64_t off = P.c_row0 * P.c_ldd + (col - qb * P.c_fc);
+          for (int d = 0; d < P.c_dup; ++d) {
+            float* rb = col_ok ? P.c_tab[qb * P.c_dup + d] + off : nullptr;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int rl = i * 4 + rr;
+              float4 v;
+              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                           : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                           : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
+              v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+              if (P.relu) {
+                v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
+                v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
+              }
+              const int row = row0 + rl;
+              if (row < P.M && col_ok)
+                *reinterpret_cast<float4*>(rb + (int64_t)row * P.c_ldd) = v;
             }
           }
         }
@@ -586,6 +606,7 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
   P.N = (int)N;
   P.K = (int)K;
   P.a_kw = (int)a_kw;
+  P.a_3d = a_slices > 1;
   P.BN = Np < 256 ? Np : 256;
   P.n_tiles = (int)ceil_div(Np, P.BN);
   int sms = 148;
@@ -624,7 +645,8 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
   const size_t smem = stages * stage_bytes + kEpiBytes + 1024;
 
   CUtensorMap mapA, mapBh, mapBl;
-  int rc = make_map_a(&mapA, A, M, a_kw, lda, a_slices, a_plane, mh * kBM, bk);
+  int rc = a_slices > 1 ? make_map_a(&mapA, A, M, a_kw, lda, a_slices, a_plane, mh * kBM, bk)
+                        : make_map(&mapA, A, M, K, lda, mh * kBM, bk);
   if (rc) return rc;
   rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN, bk);
   if (rc) return rc;

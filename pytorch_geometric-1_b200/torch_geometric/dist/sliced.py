@@ -214,7 +214,7 @@ class PeerTransport(object):
     _FLAG_BYTES = 1024                  # 64 ranks x 8-byte epoch flags at the head of the arena
     FENCE_TIMEOUT_NS = 20 * 10 ** 9
 
-    def __init__(self, plan, device, group=None, fence_mode='flags'):
+    def __init__(self, plan, device, group=None, fence_mode='nccl'):
         from .. import _native as nat
         self.fence_mode = fence_mode
         self.nat = nat
@@ -435,7 +435,7 @@ class SlicedGraph(object):
     graph when there is one row group — plus the row block / column slice bookkeeping."""
 
     def __init__(self, edge_index, norm, num_nodes, rank, world_size, group=None, i=1,
-                 transport='peer', build_adj=True, row_groups=1, fence_mode='flags'):
+                 transport='peer', build_adj=True, row_groups=1, fence_mode='nccl'):
         self.plan = p = SlicePlan(num_nodes, world_size, rank, row_groups)
         self.i = i
         self.device = edge_index.device
