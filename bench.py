@@ -160,6 +160,12 @@ def cpu_reference(steps, warmup, sample='products_small'):
     return value, dt / steps * 1e3, cores, desc, e_prime
 
 
+def workload_text(n, pairs, e_prime):
+    return ('3-layer GCNConv (100->256->256->47, cached=True, relu) forward on the synthetic '
+            'products-shaped power-law graph: %d nodes, %d directed edges, %d after self-loops '
+            '(BASELINE configs[4])' % (n, 2 * pairs, e_prime))
+
+
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
@@ -167,12 +173,17 @@ def run_reference(args):
     steps = max(1, min(args.steps, 3))
     warmup = max(1, min(args.warmup, 1))
     value, ms, cores, desc, _ = cpu_reference(steps, warmup)
+    n, pairs, _, _, _ = WORKLOADS[args.workload]
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': steps, 'warmup': warmup, 'ms_per_step': ms, 'higher_is_better': True,
         'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': '3-layer GCNConv hidden 256, products-shaped power-law graph '
-                               '(BASELINE configs[4]); bounded sample: ' + desc},
+        # same workload as the B200 arm; every step is a bounded sample of it (the generator
+        # adds no self-loops or duplicates, so E' = 2 * pairs + nodes)
+        'config': {'workload': workload_text(n, pairs, 2 * pairs + n), 'name': args.workload,
+                   'edges_per_step': 3 * (2 * pairs + n),
+                   'parallelism': 'host cores (%d threads)' % cores,
+                   'sample': desc},
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port',
                          'sample': desc},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
@@ -509,10 +520,7 @@ def run_b200(args):
             'warmup': max(args.warmup, 3), 'ms_per_step': ms_per_step, 'higher_is_better': True,
             'scaling': 'strong', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
             'config': {
-                'workload': '3-layer GCNConv (100->256->256->47, cached=True, relu) forward on the '
-                            'synthetic products-shaped power-law graph: %d nodes, %d directed '
-                            'edges, %d after self-loops (BASELINE configs[4])' %
-                            (n, 2 * pairs, e_prime),
+                'workload': workload_text(n, pairs, e_prime),
                 'name': args.workload,
                 'edges_per_step': 3 * e_prime,
                 'parallelism': 'single GPU' if world == 1 else
