@@ -60,14 +60,16 @@ class CSR(object):
             self._items[t] = plan
         return plan
 
-    def flagged(self, which):
-        """``col`` or ``perm`` with bit 31 set on the last slot of every row (the
-        index stream of the streaming kernels); built once, cached."""
+    def flagged(self, which, idx=None):
+        """``col``, ``perm`` or a caller-supplied int32 index ``idx`` (cached under the name
+        ``which``) with bit 31 set on the last slot of every row — the index stream of the
+        streaming kernels; built once, cached."""
         key = ('flag', which)
         hit = self._items.get(key)
         if hit is not None:
             return hit
-        idx = self.col if which == 'col' else self.perm
+        if idx is None:
+            idx = self.col if which == 'col' else self.perm
         out = torch.empty_like(idx)
         if self.E > 0:
             nat.call('pygb_seg_flag_idx', idx.device, nat.ptr(self.rowptr), self.n_rows,
@@ -178,6 +180,7 @@ class Adj(object):
                              self.size[self.j])
         self._src = None
         self._wcache = {}
+        self._idx = {}
 
     @property
     def n_dst(self):
@@ -193,6 +196,27 @@ class Adj(object):
             ei = self.edge_index
             self._src = build_csr(ei[self.j], ei[self.i], self.size[self.j], self.size[self.i])
         return self._src
+
+    @property
+    def iota(self):
+        """0..E-1 (int32): the identity index over the slots of a sorted graph."""
+        hit = self._idx.get('iota')
+        if hit is None:
+            hit = torch.arange(self.E, dtype=torch.int32, device=self.edge_index.device)
+            self._idx['iota'] = hit
+        return hit
+
+    @property
+    def src_to_dst_slot(self):
+        """For slot p of the source-sorted graph, the slot of the same edge in the
+        destination-sorted graph (int32 [E]); built once."""
+        hit = self._idx.get('s2d')
+        if hit is None:
+            inv = torch.empty(self.E, dtype=torch.int32, device=self.edge_index.device)
+            inv[self.dst.perm.long()] = self.iota
+            hit = inv[self.src.perm.long()].contiguous()
+            self._idx['s2d'] = hit
+        return hit
 
     def permuted(self, w, which):
         """``w[perm]`` for the 'dst' or 'src' order, memoised per weight tensor."""

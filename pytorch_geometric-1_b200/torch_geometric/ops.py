@@ -59,8 +59,9 @@ def _f32(t):
 # raw (no autograd) launches
 # --------------------------------------------------------------------------
 def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=None,
-                          heads=None):
-    """out[i] = reduce_p w_p * x[idx[p]] over the rows of ``csr``."""
+                          heads=None, idx_key=None):
+    """out[i] = reduce_p w_p * x[idx[p]] over the rows of ``csr``.  ``idx`` is ``csr.col``,
+    ``csr.perm`` or — with a cache key ``idx_key`` — any int32 ``[E]`` index in slot order."""
     dev = nat.require_cuda(x, idx, w, bias)
     x2 = _rows2d(x)
     F = x2.size(1)
@@ -88,8 +89,11 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
             idxf = csr.flagged('col')
         elif idx is csr.perm:
             idxf = csr.flagged('perm')
+        elif idx_key is not None:
+            idxf = csr.flagged(idx_key, idx)
         else:
-            raise ValueError('seg_gather_reduce_raw: idx must be csr.col or csr.perm')
+            raise ValueError('seg_gather_reduce_raw: idx must be csr.col or csr.perm '
+                             '(or come with an idx_key)')
         ws_bytes = nat.workspace('pygb_seg_stream_workspace', dt, n_sub, F)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         nat.call('pygb_seg_gather_reduce_stream', dev, nat.MEAN if reduce == 'mean' else nat.SUM,
@@ -468,25 +472,28 @@ class _GATFused(torch.autograd.Function):
         xs = _f32(_rows2d(x_src))
         outf = _f32(out)
         E = adj.E
+        # alpha and ds per (edge, head) in the slot order of the destination-sorted graph:
+        # coalesced writes, and the sums over a destination row read consecutive slots
         alpha = torch.empty((E, H), dtype=torch.float32, device=dev)
         ds = torch.empty((E, H), dtype=torch.float32, device=dev)
         dst = adj.dst
         if adj.n_dst > 0 and E > 0:
             nat.call('pygb_gat_edge_grad', dev, nat.ptr(xs), _ld(xs), nat.ptr(a_src),
                      nat.ptr(a_dst), H, C, float(slope), nat.ptr(dst.rowptr), nat.ptr(dst.col),
-                     nat.ptr(dst.perm), adj.n_dst, nat.ptr(outf), F, nat.ptr(bias2), nat.ptr(gf),
+                     None, adj.n_dst, nat.ptr(outf), F, nat.ptr(bias2), nat.ptr(gf),
                      _ld(gf), nat.ptr(row_max), nat.ptr(row_sum), nat.ptr(alpha), nat.ptr(ds))
         src = adj.src
+        s2d = adj.src_to_dst_slot                     # slot of the source-sorted graph -> dst slot
         # d_xw[j] = sum_p alpha_p * g[dst_p]   (transposed walk, per-head weights)
-        d_xs = seg_gather_reduce_raw(gf, src, src.col, 'sum', alpha, src.perm, None, (H, C))
-        d_a_src = seg_gather_reduce_raw(ds, src, src.perm, 'sum')          # [n_src, H]
+        d_xs = seg_gather_reduce_raw(gf, src, src.col, 'sum', alpha, s2d, None, (H, C))
+        d_a_src = seg_gather_reduce_raw(ds, src, s2d, 'sum', idx_key='s2d')   # [n_src, H]
         att_d, att_s = att2[:, :C], att2[:, C:]
         d_xs = d_xs.view(-1, H, C) + d_a_src.unsqueeze(-1) * att_s.unsqueeze(0)
         d_att_s = torch.einsum('nh,nhc->hc', d_a_src, xs.view(-1, H, C))
         d_xd = None
         d_att_d = torch.zeros_like(d_att_s)
         if a_dst is not None:
-            d_a_dst = seg_gather_reduce_raw(ds, dst, dst.perm, 'sum')      # [n_dst, H]
+            d_a_dst = seg_gather_reduce_raw(ds, dst, adj.iota, 'sum', idx_key='iota')   # [n_dst, H]
             xd = xs if ctx.same else _f32(_rows2d(x_dst))
             d_att_d = torch.einsum('nh,nhc->hc', d_a_dst, xd.view(-1, H, C))
             dd = d_a_dst.unsqueeze(-1) * att_d.unsqueeze(0)

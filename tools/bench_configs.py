@@ -98,11 +98,22 @@ def cfg3(dev, iters):
     n, H, C = data.x.size(0), 8, 8
     t = timeit(fwd, iters)
     bd = breakdown(fwd)
+    xg = data.x.clone().requires_grad_(True)
+
+    def fwdbwd():
+        xg.grad = None
+        for p_ in gat.parameters():
+            p_.grad = None
+        gat(xg, data.edge_index).square().sum().backward()
+
+    t_fb = timeit(fwdbwd, max(iters // 2, 2))
+    bd_fb = breakdown(fwdbwd)
     k2 = bd.get('pygb_gat_forward_stream', bd.get('pygb_gat_forward', None))
     k2_bytes = e_prime * (4 + 4 * H + 4 * H * C) + n * H * C * 4 + 2 * n * H * 4 + (n + 1) * 4
     return {'cfg': 3, 'workload': 'GATConv 8x8, Reddit-shaped (%d nodes, %d edges, %d after '
             'remove+add self-loops, 602 feats)' % (n, data.edge_index.size(1), e_prime),
             'fwd_ms': round(t, 4), 'fwd_edges_per_s': e_prime / t * 1e3, 'breakdown_ms': bd,
+            'fwd_bwd_ms': round(t_fb, 4), 'fwd_bwd_breakdown_ms': bd_fb,
             'k2_algorithmic_bytes': k2_bytes,
             'k2_GBps': (k2_bytes / k2 / 1e6) if k2 else None}
 
