@@ -81,6 +81,15 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
     w = _f32(w)
     bias = _f32(bias)
     ldx = _ld(x2)
+    if (heads is None and wperm is None and STREAM and F > 1
+            and (x2.data_ptr() % 16 or ldx % vec or ldx < ldo)):
+        # rows that are not 16-byte multiples (e.g. a contiguous [N, 47] gradient): one padded
+        # copy (2 passes over N*F) buys the streaming kernel (vs ~3x slower per-row kernel)
+        xp = torch.empty((x2.size(0), ldo), dtype=x2.dtype, device=dev)
+        xp[:, :F].copy_(x2)
+        if ldo > F:
+            xp[:, F:].zero_()
+        x2, ldx = xp, ldo
     if (heads is None and wperm is None and STREAM and F > 1 and x2.data_ptr() % 16 == 0
             and ldx % vec == 0 and ldx >= ldo):
         # K1 v2: streaming kernel over equal-slot work items
@@ -588,9 +597,15 @@ class _Linear(torch.autograd.Function):
         x, w = ctx.saved_tensors
         gx = gw = gb = None
         if ctx.needs_input_grad[0]:
-            gx = torch.matmul(g, w.t())
+            wt = w.t().contiguous()
+            g2 = g if g.stride(-1) == 1 else g.contiguous()
+            if _gemm_eligible(g2, wt):              # dX = g W^T on the same tcgen05 kernel
+                gx = gemm_xw_raw(g2, wt)
+                gx = gx if gx.is_contiguous() else gx.contiguous()
+            else:
+                gx = torch.matmul(g, w.t())
         if ctx.needs_input_grad[1]:
-            gw = torch.matmul(x.t(), g)
+            gw = torch.matmul(x.t(), g)             # reduction over the rows: library split-K GEMM
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = g.sum(0)
         return gx, gw, gb

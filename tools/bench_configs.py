@@ -145,13 +145,54 @@ def cfg4(dev, iters):
             'breakdown_ms': bd, 'k3_algorithmic_bytes': k3_bytes, 'k3_GBps': (k3_bytes / k3 / 1e6) if k3 else None}
 
 
+def cfg5(dev, iters):
+    """The bench.py workload (3-layer GCN on the products-shaped graph) as a training step."""
+    from bench import WORKLOADS
+    from torch_geometric.datasets import synthetic
+    from torch_geometric.nn import GCNConv
+    n, pairs, fin, hid, ncls = WORKLOADS['products']
+    data = synthetic.products_like(seed=4, device=dev, num_nodes=n, num_pairs=pairs, num_features=fin)
+    torch.manual_seed(0)
+    convs = [GCNConv(fin, hid, cached=True).to(dev), GCNConv(hid, hid, cached=True).to(dev),
+             GCNConv(hid, ncls, cached=True).to(dev)]
+    params = [p_ for c in convs for p_ in c.parameters()]
+
+    def net(x):
+        h = x
+        for k, c in enumerate(convs):
+            h = c(h, data.edge_index)
+            if k < 2:
+                h = F.relu(h)
+        return F.log_softmax(h, dim=1)
+
+    def fwd():
+        with torch.no_grad():
+            return net(data.x)
+
+    def fwdbwd():
+        for p_ in params:
+            p_.grad = None
+        F.nll_loss(net(data.x), data.y).backward()
+
+    fwd()
+    e_prime = convs[0].cached_result[0].size(1)
+    for c in convs[1:]:
+        c.cached_result = convs[0].cached_result
+    iters = max(iters // 2, 3)
+    t_f, t_fb = timeit(fwd, iters), timeit(fwdbwd, iters)
+    return {'cfg': 5, 'workload': '3-layer GCN 100->256->256->47, products-shaped (%d nodes, %d edges '
+            'after self-loops)' % (n, e_prime), 'fwd_ms': round(t_f, 3), 'fwd_bwd_ms': round(t_fb, 3),
+            'fwd_edges_per_s': 3 * e_prime / t_f * 1e3, 'fwd_bwd_edges_per_s': 3 * e_prime / t_fb * 1e3,
+            'fwd_bwd_breakdown_ms': breakdown(fwdbwd)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--cfg', default='2,3,4')
     ap.add_argument('--iters', type=int, default=10)
     args = ap.parse_args()
     dev = torch.device('cuda:0')
-    fns = {'2': cfg2, '3': cfg3, '4': cfg4}
+    fns = {'2': cfg2, '3': cfg3, '4': cfg4, '5': cfg5}
     for c in args.cfg.split(','):
         print(json.dumps(fns[c](dev, args.iters)), flush=True)
         torch.cuda.empty_cache()

@@ -26,6 +26,7 @@ def main():
     ap.add_argument('--iters', type=int, default=10)
     ap.add_argument('--T', default='')
     ap.add_argument('--skip-v1', action='store_true')
+    ap.add_argument('--ld', type=int, default=0, help='row stride of x in elements (0: F padded to 16 bytes)')
     args = ap.parse_args()
     from bench import WORKLOADS, k1_bytes, peaks
     from torch_geometric import ops
@@ -47,7 +48,7 @@ def main():
     Ts = [None] + [int(t) for t in args.T.split(',') if t]
     for F in [int(f) for f in args.widths.split(',')]:
         vec = 16 // (4 if dtype == torch.float32 else 2)
-        ld = (F + vec - 1) // vec * vec
+        ld = max(args.ld, (F + vec - 1) // vec * vec)
         x = torch.randn(n, ld, device=dev, dtype=torch.float32).to(dtype)[:, :F]
         nbytes = k1_bytes(E, n, F, x.element_size())
         variants = [] if args.skip_v1 else [('v1', False, None)]
