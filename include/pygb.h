@@ -285,6 +285,33 @@ int pygb_gat_edge_grad(const float* xw, int64_t ldx, const float* a_src,
                        const float* grad_out, int64_t ldg, const float* row_max,
                        const float* row_sum, float* alpha, float* ds, pygb_stream_t s);
 
+/* Streaming GAT backward (autograd of A.10 / A.7; fp32): alpha and ds are RECOMPUTED
+ * from per-node records in both passes, so no [E,H] tensor is written or read.
+ *   pygb_gat_backward_prep: rec[i,h] = (a_dst[i,h] (0 if a_dst == NULL),
+ *       row_max[i,h] * log2(e), 1 / (row_sum[i,h] + 1e-16), <g[i,h,:], out[i,h,:] - bias[h,:]>)
+ *       as float[n_dst, H, 4] (16-byte aligned).
+ *   pygb_gat_backward_stream, mode 0: destination-sorted walk (rowptr / idx_flagged /
+ *       nz_rows / sub_info of the dst CSR; row_feat = grad_out [n_dst, H*C], gat_feat = xw):
+ *       d_a[i,h] = d a_dst = sum over the in-edges of i of ds;  d_feat unused (NULL).
+ *   mode 1: source-sorted walk (tables of the src CSR; row_feat = xw [n_src, H*C],
+ *       gat_feat = grad_out): d_feat[j,:] = sum_i alpha_ij g[i,:],  d_a[j,h] = d a_src.
+ * ds = alpha (<g_i, xw_j>_h - rec.w) * leaky_relu'(a_dst + a_src).  Sums run in slot
+ * order, cut rows are combined by a fix-up kernel: deterministic, no atomics.  Rows
+ * without a slot get 0.  Needs C in {4,8,...,128}, H*C <= 512, 16-byte aligned rows
+ * (else PYGB_E_UNSUPPORTED: the caller uses pygb_gat_edge_grad). */
+int pygb_gat_backward_prep(const float* a_dst, const float* row_max, const float* row_sum,
+                           const float* out, int64_t ldo, const float* bias,
+                           const float* grad_out, int64_t ldg, int64_t n_dst, int H, int C,
+                           float* rec, pygb_stream_t s);
+size_t pygb_gat_backward_stream_workspace(int mode, int64_t n_sub, int H, int C);
+int pygb_gat_backward_stream(int mode, const float* row_feat, int64_t ld_row,
+                             const float* gat_feat, int64_t ld_gat, const float* a_src,
+                             const float* rec, int H, int C, float negative_slope,
+                             const int32_t* rowptr, const int32_t* idx_flagged, int64_t n_rows,
+                             int64_t E, const int32_t* nz_rows, const int32_t* sub_info,
+                             int32_t Ts, int64_t n_sub, float* d_feat, int64_t ldd, float* d_a,
+                             void* ws, size_t ws_bytes, pygb_stream_t s);
+
 /* ---- K5: dense node-feature transform on the tensor cores ------------------ */
 
 /* C[M,N] = A[M,K] . W[K,N] (+ bias[N]), fp32 in / fp32 out — the

@@ -64,6 +64,10 @@ SIGNATURES = {
     'pygb_gat_stream_workspace': (_Z, [_L, _I, _I]),
     'pygb_gat_forward_stream': (_I, [_I, _P, _L, _P, _P, _I, _I, _F, _P, _P, _L, _L, _P, _P, _I, _L,
                                      _P, _P, _L, _P, _P, _P, _Z, _P]),
+    'pygb_gat_backward_prep': (_I, [_P, _P, _P, _P, _L, _P, _P, _L, _L, _I, _I, _P, _P]),
+    'pygb_gat_backward_stream_workspace': (_Z, [_I, _L, _I, _I]),
+    'pygb_gat_backward_stream': (_I, [_I, _P, _L, _P, _L, _P, _P, _I, _I, _F, _P, _P, _L, _L, _P, _P,
+                                      _I, _L, _P, _L, _P, _P, _Z, _P]),
     'pygb_gat_alpha': (_I, [_P, _P, _I, _F, _P, _P, _P, _L, _P, _P, _P, _P]),
     'pygb_gemm_weight_workspace': (_Z, [_L, _L]),
     'pygb_gemm_xw': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _P, _Z, _P]),

@@ -481,28 +481,57 @@ class _GATFused(torch.autograd.Function):
         xs = _f32(_rows2d(x_src))
         outf = _f32(out)
         E = adj.E
-        # alpha and ds per (edge, head) in the slot order of the destination-sorted graph:
-        # coalesced writes, and the sums over a destination row read consecutive slots
-        alpha = torch.empty((E, H), dtype=torch.float32, device=dev)
-        ds = torch.empty((E, H), dtype=torch.float32, device=dev)
-        dst = adj.dst
-        if adj.n_dst > 0 and E > 0:
-            nat.call('pygb_gat_edge_grad', dev, nat.ptr(xs), _ld(xs), nat.ptr(a_src),
-                     nat.ptr(a_dst), H, C, float(slope), nat.ptr(dst.rowptr), nat.ptr(dst.col),
-                     None, adj.n_dst, nat.ptr(outf), F, nat.ptr(bias2), nat.ptr(gf),
-                     _ld(gf), nat.ptr(row_max), nat.ptr(row_sum), nat.ptr(alpha), nat.ptr(ds))
-        src = adj.src
-        s2d = adj.src_to_dst_slot                     # slot of the source-sorted graph -> dst slot
-        # d_xw[j] = sum_p alpha_p * g[dst_p]   (transposed walk, per-head weights)
-        d_xs = seg_gather_reduce_raw(gf, src, src.col, 'sum', alpha, s2d, None, (H, C))
-        d_a_src = seg_gather_reduce_raw(ds, src, s2d, 'sum', idx_key='s2d')   # [n_src, H]
+        dst, src = adj.dst, adj.src
+        lh = C // 4
+        d_a_dst = None
+        if (STREAM and adj.n_dst > 0 and E > 0 and C % 4 == 0 and lh & (lh - 1) == 0 and lh <= 32
+                and F // 4 <= 128 and _ld(xs) % 4 == 0 and _ld(gf) % 4 == 0
+                and xs.data_ptr() % 16 == 0 and gf.data_ptr() % 16 == 0):
+            # streaming backward: alpha / ds are recomputed from per-node records in both
+            # walks, no [E, H] tensor exists (csrc/gat_bwd_stream.cu)
+            rec = torch.empty((adj.n_dst, H, 4), dtype=torch.float32, device=dev)
+            nat.call('pygb_gat_backward_prep', dev, nat.ptr(a_dst), nat.ptr(row_max),
+                     nat.ptr(row_sum), nat.ptr(outf), _ld(outf), nat.ptr(bias2), nat.ptr(gf),
+                     _ld(gf), adj.n_dst, H, C, nat.ptr(rec))
+
+            def walk(mode, csr, row_feat, gat_feat, d_feat, d_a):
+                Ts, n_sub, nz_rows, sub_info = csr.items(STREAM_T)
+                ws_bytes = nat.workspace('pygb_gat_backward_stream_workspace', mode, n_sub, H, C)
+                ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+                nat.call('pygb_gat_backward_stream', dev, mode, nat.ptr(row_feat), _ld(row_feat),
+                         nat.ptr(gat_feat), _ld(gat_feat), nat.ptr(a_src), nat.ptr(rec), H, C,
+                         float(slope), nat.ptr(csr.rowptr), nat.ptr(csr.flagged('col')),
+                         csr.n_rows, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub,
+                         nat.ptr(d_feat), F, nat.ptr(d_a), nat.ptr(ws), ws_bytes)
+
+            if a_dst is not None:
+                d_a_dst = torch.empty((adj.n_dst, H), dtype=torch.float32, device=dev)
+                walk(0, dst, gf, xs, None, d_a_dst)
+            d_xs = torch.empty((adj.n_src, F), dtype=torch.float32, device=dev)
+            d_a_src = torch.empty((adj.n_src, H), dtype=torch.float32, device=dev)
+            walk(1, src, xs, gf, d_xs, d_a_src)
+        else:
+            # alpha and ds per (edge, head) in the slot order of the destination-sorted graph:
+            # coalesced writes, and the sums over a destination row read consecutive slots
+            alpha = torch.empty((E, H), dtype=torch.float32, device=dev)
+            ds = torch.empty((E, H), dtype=torch.float32, device=dev)
+            if adj.n_dst > 0 and E > 0:
+                nat.call('pygb_gat_edge_grad', dev, nat.ptr(xs), _ld(xs), nat.ptr(a_src),
+                         nat.ptr(a_dst), H, C, float(slope), nat.ptr(dst.rowptr), nat.ptr(dst.col),
+                         None, adj.n_dst, nat.ptr(outf), F, nat.ptr(bias2), nat.ptr(gf),
+                         _ld(gf), nat.ptr(row_max), nat.ptr(row_sum), nat.ptr(alpha), nat.ptr(ds))
+            s2d = adj.src_to_dst_slot                 # slot of the source-sorted graph -> dst slot
+            # d_xw[j] = sum_p alpha_p * g[dst_p]   (transposed walk, per-head weights)
+            d_xs = seg_gather_reduce_raw(gf, src, src.col, 'sum', alpha, s2d, None, (H, C))
+            d_a_src = seg_gather_reduce_raw(ds, src, s2d, 'sum', idx_key='s2d')   # [n_src, H]
+            if a_dst is not None:
+                d_a_dst = seg_gather_reduce_raw(ds, dst, adj.iota, 'sum', idx_key='iota')
         att_d, att_s = att2[:, :C], att2[:, C:]
         d_xs = d_xs.view(-1, H, C) + d_a_src.unsqueeze(-1) * att_s.unsqueeze(0)
         d_att_s = torch.einsum('nh,nhc->hc', d_a_src, xs.view(-1, H, C))
         d_xd = None
         d_att_d = torch.zeros_like(d_att_s)
         if a_dst is not None:
-            d_a_dst = seg_gather_reduce_raw(ds, dst, adj.iota, 'sum', idx_key='iota')   # [n_dst, H]
             xd = xs if ctx.same else _f32(_rows2d(x_dst))
             d_att_d = torch.einsum('nh,nhc->hc', d_a_dst, xd.view(-1, H, C))
             dd = d_a_dst.unsqueeze(-1) * att_d.unsqueeze(0)

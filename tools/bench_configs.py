@@ -39,6 +39,8 @@ def breakdown(fn):
     log, nat.event_log = nat.event_log, None
     agg = {}
     for name, a, e0, e1 in log:
+        if name == 'pygb_gat_backward_stream':
+            name += ':mode%d' % a[0]          # 0 = destination-sorted walk, 1 = source-sorted
         agg[name] = agg.get(name, 0.0) + e0.elapsed_time(e1)
     return {k: round(v, 4) for k, v in sorted(agg.items(), key=lambda kv: -kv[1])}
 
