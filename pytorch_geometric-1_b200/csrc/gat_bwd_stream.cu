@@ -83,7 +83,8 @@ __device__ __forceinline__ float lds_f32_b(uint32_t a) {
   return r;
 }
 
-template <int MODE, int LPF, int VPL, bool EXACT>
+// LHT = lanes per head known at compile time (1, 2, 4) or 0: read P.LH.
+template <int MODE, int LPF, int VPL, bool EXACT, int LHT>
 __global__ void __launch_bounds__(kStreamWarps * 32)
 gat_bwd_stream_kernel(const GatBwdParams P) {
   using Cf = BwdCfg<MODE, LPF, VPL>;
@@ -91,19 +92,34 @@ gat_bwd_stream_kernel(const GatBwdParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int fl = lane & (LPF - 1), es = lane / LPF;
-  const uint32_t wbase = (uint32_t)__cvta_generic_to_shared(smem_raw) + (uint32_t)(warp * Cf::WARP_B);
+  const int F = P.F, H = P.H, LH = LHT ? LHT : P.LH;
+  // mode 1 stages ONE 16-byte record per (slot, head), copied by the first lane of the
+  // head and read by all its lanes; mode 0 stages a_src[j, head] per lane (4 bytes)
+  const int side_b = MODE == kModeSrc ? EPW * H * 16 : Cf::SIDE_B;
+  const int stage_b = G * (Cf::DATA_B + side_b) + Cf::META_B;
+  const uint32_t wbase =
+      (uint32_t)__cvta_generic_to_shared(smem_raw) + (uint32_t)(warp * NSTAGE * stage_b);
   const uint32_t data0 = wbase + (uint32_t)(lane * 16);
-  const uint32_t side0 = wbase + (uint32_t)(G * Cf::DATA_B + lane * Cf::SIDE_SZ);
-  const uint32_t meta0 = wbase + (uint32_t)(G * (Cf::DATA_B + Cf::SIDE_B) + es * G * 4);
-  const int F = P.F, H = P.H, LH = P.LH;
+  const uint32_t meta0 = wbase + (uint32_t)(G * (Cf::DATA_B + side_b) + es * G * 4);
   const int units = F / KV;
-  bool act[VPL];
+  bool act[VPL], lead_h[VPL];
   int head[VPL];
+  uint32_t side0[VPL];
+  const char* sideg[VPL];  // global base of the staged side operand of unit v
 #pragma unroll
   for (int v = 0; v < VPL; ++v) {
     act[v] = EXACT || (fl + v * LPF < units);
     head[v] = act[v] ? ((fl + v * LPF) * KV) / P.C : 0;
+    lead_h[v] = act[v] && ((fl + v * LPF) & (LH - 1)) == 0;
+    if (MODE == kModeSrc) {
+      side0[v] = wbase + (uint32_t)(G * Cf::DATA_B + (es * H + head[v]) * 16);
+      sideg[v] = reinterpret_cast<const char*>(P.rec) + head[v] * 16;
+    } else {
+      side0[v] = wbase + (uint32_t)(G * Cf::DATA_B + lane * 4 + v * 128);
+      sideg[v] = reinterpret_cast<const char*>(P.a_src) + head[v] * 4;
+    }
   }
+  const uint32_t ldside = (uint32_t)(MODE == kModeSrc ? H * 16 : H * 4);
   const int W = gridDim.x * kStreamWarps;
   const char* gb = reinterpret_cast<const char*>(P.gat_feat) + fl * 16;
   asm volatile("" : "+l"(gb));
@@ -215,36 +231,35 @@ gat_bwd_stream_kernel(const GatBwdParams P) {
       const int nstages = (nsteps + G - 1) / G;
 
       auto issue_stage = [&](int st) {
-        const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * Cf::STAGE_B);
+        const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * stage_b);
         const int k0 = st * G;
         if (st > 0 && (k0 & (LPF - 1)) == 0) {
           idx_cur = idx_nxt;
           idx_nxt = (FULL ? k0 + LPF < Ts : k0 + LPF + fl < n_g) ? __ldg(my_idx + k0 + LPF) : 0;
         }
         int craw[G];
-        const char* src[G];
-        uint64_t node[G];
+        uint32_t c[G];
         const int lane0 = grp_lane0 + (k0 & (LPF - 1));
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           craw[g] = __shfl_sync(kFull, idx_cur, lane0 + g);
-          const uint32_t c = (uint32_t)(craw[g] & 0x7fffffff);
-          src[g] = gb + (uint64_t)c * ldgb;
-          node[g] = (uint64_t)c * H;
+          c[g] = (uint32_t)(craw[g] & 0x7fffffff);
         }
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           if (FULL || k0 + g < n_g) {
 #pragma unroll
             for (int v = 0; v < VPL; ++v) {
-              if (act[v]) {
-                cp_async16(data0 + so + (uint32_t)(g * Cf::DATA_B + v * 512), src[g] + v * LPF * 16);
-                if (MODE == kModeSrc)
-                  cp_async16(side0 + so + (uint32_t)(g * Cf::SIDE_B + v * 512),
-                             rec + node[g] + head[v]);
-                else
-                  cp_async_small<4>(side0 + so + (uint32_t)(g * Cf::SIDE_B + v * 128),
-                                    a_src + node[g] + head[v]);
+              if (act[v])
+                cp_async16(data0 + so + (uint32_t)(g * Cf::DATA_B + v * 512),
+                           gb + (uint64_t)c[g] * ldgb + v * LPF * 16);
+              if (MODE == kModeSrc) {
+                if (lead_h[v])
+                  cp_async16(side0[v] + so + (uint32_t)(g * side_b),
+                             sideg[v] + (uint64_t)c[g] * ldside);
+              } else if (act[v]) {
+                cp_async_small<4>(side0[v] + so + (uint32_t)(g * side_b),
+                                  sideg[v] + (uint64_t)c[g] * ldside);
               }
             }
           }
@@ -254,7 +269,7 @@ gat_bwd_stream_kernel(const GatBwdParams P) {
       };
 
       auto consume_stage = [&](int st) {
-        const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * Cf::STAGE_B);
+        const uint32_t so = (uint32_t)((st & (NSTAGE - 1)) * stage_b);
         const int k0 = st * G;
         uint32_t flags[G];
         lds_words<G>(meta0 + so, flags);
@@ -273,11 +288,11 @@ gat_bwd_stream_kernel(const GatBwdParams P) {
               f[2] = __uint_as_float(qv.z), f[3] = __uint_as_float(qv.w);
               float sv, m2, inv;
               if (MODE == kModeSrc) {
-                const uint4 rq = lds128(side0 + so + (uint32_t)(g * Cf::SIDE_B + v * 512));
+                const uint4 rq = lds128(side0[v] + so + (uint32_t)(g * side_b));
                 sv = __uint_as_float(rq.x) + rs[v][0];
                 m2 = __uint_as_float(rq.y), inv = __uint_as_float(rq.z), rdot = __uint_as_float(rq.w);
               } else {
-                sv = rs[v][0] + lds_f32_b(side0 + so + (uint32_t)(g * Cf::SIDE_B + v * 128));
+                sv = rs[v][0] + lds_f32_b(side0[v] + so + (uint32_t)(g * side_b));
                 m2 = rs[v][1], inv = rs[v][2], rdot = rs[v][3];
               }
               const bool pos = sv > 0.f;
@@ -287,7 +302,12 @@ gat_bwd_stream_kernel(const GatBwdParams P) {
               dot = fmaf(f[3], rf[v][3], fmaf(f[2], rf[v][2], fmaf(f[1], rf[v][1], f[0] * rf[v][0])));
             }
             // <g_i, xw_j> over the C channels of the head: LH adjacent lanes
-            for (int o = 1; o < LH; o <<= 1) dot += __shfl_xor_sync(kFull, dot, o);
+            if (LHT) {
+#pragma unroll
+              for (int o = 1; o < LHT; o <<= 1) dot += __shfl_xor_sync(kFull, dot, o);
+            } else {
+              for (int o = 1; o < LH; o <<= 1) dot += __shfl_xor_sync(kFull, dot, o);
+            }
             if (on) {
               da[v] = fmaf(alpha * dlr, dot - rdot, da[v]);
               if (MODE == kModeSrc) {
@@ -392,26 +412,32 @@ gat_bwd_prep_kernel(const float* __restrict__ a_dst, const float* __restrict__ r
   }
 }
 
-template <int MODE, int LPF, int VPL, bool EXACT>
+template <int MODE, int LPF, int VPL, bool EXACT, int LHT>
 int launch_bwd_k(const GatBwdParams& P, cudaStream_t st) {
   using Cf = BwdCfg<MODE, LPF, VPL>;
-  auto kern = gat_bwd_stream_kernel<MODE, LPF, VPL, EXACT>;
+  auto kern = gat_bwd_stream_kernel<MODE, LPF, VPL, EXACT, LHT>;
+  // same geometry as the kernel: the side operand of mode 1 is H records per slot
+  const int side_b = MODE == kModeSrc ? Cf::EPW * P.H * 16 : Cf::SIDE_B;
+  const int cta_b = Cf::NSTAGE * (Cf::G * (Cf::DATA_B + side_b) + Cf::META_B) * kStreamWarps;
   static std::mutex mu;
-  static int ctas_cache[64] = {0};
+  static int ctas_cache[64] = {0}, smem_cache[64] = {0};
   int dev = 0;
   PYGB_CUDA(cudaGetDevice(&dev));
   int ctas_per_sm = 0;
   cudaError_t attr_err = cudaSuccess;
   {
     std::lock_guard<std::mutex> lock(mu);
-    if (dev >= 0 && dev < 64) ctas_per_sm = ctas_cache[dev];
+    if (dev >= 0 && dev < 64 && smem_cache[dev] == cta_b) ctas_per_sm = ctas_cache[dev];
     if (ctas_per_sm == 0) {
       attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cf::CTA_B);
       if (attr_err == cudaSuccess)
         attr_err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, kern,
-                                                                 kStreamWarps * 32, Cf::CTA_B);
+                                                                 kStreamWarps * 32, cta_b);
       if (ctas_per_sm < 1) ctas_per_sm = 1;
-      if (attr_err == cudaSuccess && dev >= 0 && dev < 64) ctas_cache[dev] = ctas_per_sm;
+      if (attr_err == cudaSuccess && dev >= 0 && dev < 64) {
+        ctas_cache[dev] = ctas_per_sm;
+        smem_cache[dev] = cta_b;
+      }
     }
   }
   PYGB_CUDA(attr_err);
@@ -420,15 +446,25 @@ int launch_bwd_k(const GatBwdParams& P, cudaStream_t st) {
   const int64_t need = ceil_div(n_items, kStreamWarps);
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  kern<<<(unsigned)grid, kStreamWarps * 32, Cf::CTA_B, st>>>(P);
+  kern<<<(unsigned)grid, kStreamWarps * 32, cta_b, st>>>(P);
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }
 
+template <int MODE, int LPF, int VPL, bool EXACT>
+int launch_bwd_lh(const GatBwdParams& P, cudaStream_t st) {
+  switch (P.LH) {  // C = 4, 8, 16 get the unrolled head reduction
+    case 1: return launch_bwd_k<MODE, LPF, VPL, EXACT, 1>(P, st);
+    case 2: return launch_bwd_k<MODE, LPF, VPL, EXACT, 2>(P, st);
+    case 4: return launch_bwd_k<MODE, LPF, VPL, EXACT, 4>(P, st);
+    default: return launch_bwd_k<MODE, LPF, VPL, EXACT, 0>(P, st);
+  }
+}
+
 template <int MODE, int LPF, int VPL>
 int launch_bwd_one(const GatBwdParams& P, cudaStream_t st) {
-  if (P.F / 4 == LPF * VPL) return launch_bwd_k<MODE, LPF, VPL, true>(P, st);
-  return launch_bwd_k<MODE, LPF, VPL, false>(P, st);
+  if (P.F / 4 == LPF * VPL) return launch_bwd_lh<MODE, LPF, VPL, true>(P, st);
+  return launch_bwd_lh<MODE, LPF, VPL, false>(P, st);
 }
 
 template <int MODE>
