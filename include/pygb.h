@@ -285,7 +285,9 @@ int pygb_gat_edge_grad(const float* xw, int64_t ldx, const float* a_src,
                        const float* grad_out, int64_t ldg, const float* row_max,
                        const float* row_sum, float* alpha, float* ds, pygb_stream_t s);
 
-/* Streaming GAT backward (autograd of A.10 / A.7; fp32): alpha and ds are RECOMPUTED
+/* Streaming GAT backward (autograd of A.10 / A.7, fp32; what `loss.backward()` at
+ * examples/gcn.py:39 / ConvexPruning.py:386 runs through GATConv — the transposes of
+ * index_select and scatter_add plus the softmax backward): alpha and ds are RECOMPUTED
  * from per-node records in both passes, so no [E,H] tensor is written or read.
  *   pygb_gat_backward_prep: rec[i,h] = (a_dst[i,h] (0 if a_dst == NULL),
  *       row_max[i,h] * log2(e), 1 / (row_sum[i,h] + 1e-16), <g[i,h,:], out[i,h,:] - bias[h,:]>)
