@@ -197,3 +197,46 @@ def test_gat_fused_matches_unfused_full_size(dev, big):
     ref = torch.zeros(rows.numel(), H, C, dtype=torch.float64, device=dev)
     ref.index_add_(0, pos[ei2[1][e]], alpha[e].double().unsqueeze(-1) * x3[ei2[0][e]].double())
     assert_close(out[rows].view(-1, H, C), ref, 2e-5, 'fused GAT vs unfused')
+
+
+def test_gat_backward_stream_full_size(dev, big):
+    """Streaming GAT backward (two walks, alpha / ds recomputed) at full size: bit-identical
+    from run to run, equal to the per-edge kernels it replaces, and consistent with the
+    forward through a directional derivative <dL/dx, v> ~ (L(x + hv) - L(x - hv)) / 2h for a
+    linear loss L = <out, g> evaluated in the forward kernel."""
+    from torch_geometric import ops
+    adj = big['adj']
+    H, C = 4, 8
+    gen = torch.Generator(device=dev).manual_seed(9)
+    xw0 = torch.randn(N, H * C, generator=gen, device=dev)
+    att0 = torch.randn(1, H, 2 * C, generator=gen, device=dev) * 0.5
+    g = torch.randn(N, H * C, generator=gen, device=dev)
+    old_stream = ops.STREAM
+
+    def grads(stream_bwd):
+        xw = xw0.clone().requires_grad_(True)
+        att = att0.clone().requires_grad_(True)
+        ops.STREAM = True
+        out = ops.gat_propagate(xw, xw, att, None, adj, H, C, 0.2)
+        ops.STREAM = stream_bwd
+        out.backward(g)
+        return xw.grad, att.grad
+
+    try:
+        dx, datt = grads(True)
+        dx2, datt2 = grads(True)
+        assert torch.equal(dx, dx2) and torch.equal(datt, datt2), 'not deterministic'
+        dx_old, datt_old = grads(False)
+        assert_close(dx, dx_old, 2e-5, 'dx: streaming vs per-edge kernels')
+        assert_close(datt, datt_old, 2e-4, 'datt: streaming vs per-edge kernels')
+    finally:
+        ops.STREAM = old_stream
+    v = torch.randn(N, H * C, generator=gen, device=dev)
+    h = 1e-2
+    with torch.no_grad():
+        xp, xm = xw0 + h * v, xw0 - h * v
+        lp = (ops.gat_propagate(xp, xp, att0, None, adj, H, C, 0.2).double() * g).sum()
+        lm = (ops.gat_propagate(xm, xm, att0, None, adj, H, C, 0.2).double() * g).sum()
+    fd = float((lp - lm) / (2 * h))
+    an = float((dx.double() * v).sum())
+    assert abs(fd - an) <= 2e-3 * max(abs(an), 1.0) + 5e-2 * float(N) ** 0.5 * h, (fd, an)
