@@ -336,6 +336,18 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane,
                  int relu, float* C, int64_t ldc, int passes, void* ws, size_t ws_bytes,
                  pygb_stream_t s);
 
+/* dW[Kx,Ng] = X[R,Kx]^T . G[R,Ng], fp32 — the weight gradient of `torch.matmul(x,
+ * self.weight)` (what `loss.backward()` at examples/gcn.py:39 / ConvexPruning.py:386 computes
+ * for GCNConv.weight / GATConv.weight).  The reduction runs over the R rows: split-K over
+ * persistent CTAs, each accumulating its whole partial in TMEM with MN-major tcgen05.mma
+ * kind::tf32 operands (no transposed copies), partials added in CTA order (deterministic).
+ * passes as pygb_gemm_xw.  Needs Kx, Ng <= 256 and 16-byte aligned rows of X and G
+ * (else PYGB_E_UNSUPPORTED: the caller uses its library GEMM).  `ws`: the partials. */
+size_t pygb_gemm_xtg_workspace(int64_t R, int64_t Kx, int64_t Ng);
+int pygb_gemm_xtg(const float* X, int64_t ldx, const float* G, int64_t ldg, int64_t R,
+                  int64_t Kx, int64_t Ng, float* dW, int64_t ldw, int passes, void* ws,
+                  size_t ws_bytes, pygb_stream_t s);
+
 /* pygb_gemm_xw with the row layout -> column layout redistribution of the
  * feature-sliced multi-GPU layout fused into the epilogue: N is
  * N/Fc column blocks of Fc columns; element (r, q*Fc + c) of the result is stored at

@@ -490,7 +490,7 @@ EncodeTiledFn encode_fn() {
 
 // 2-D fp32 row-major [rows, cols] with row stride ld (elements); box = [box_rows, 32 cols]
 int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld,
-             int box_rows, int bk) {
+             int box_rows, int bk, bool atom32 = false) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
@@ -502,7 +502,8 @@ int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides,
                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  bk == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                         : (bk == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B),
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) for [%lld x %lld] ld %lld", (int)r,
@@ -537,6 +538,293 @@ int make_map_a(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, i
 }
 
 inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// =====================================================================================
+// K5t — dW = X^T · G : the weight gradient of X·W (autograd of A.9 / A.10, row a15).
+//
+// The reduction runs over the ROWS of X [R, Kx] and G [R, Ng] (R = 2.4 M nodes, Kx, Ng <=
+// 256), so both operands are "MN-major" for the tensor core: a TMA box of 16 rows x 32
+// floats (TMA SWIZZLE_128B_ATOM_32B) IS four canonical MN-major SW128_32B atoms (4 rows
+// of 128 bytes each; cute/atom/mma_traits_sm100.hpp, make_umma_desc<Major::MN>), so no
+// transposed copy of either matrix is made.  Split-K over persistent CTAs: CTA b owns a
+// contiguous range of 16-row steps and accumulates its whole [Kx, Ng] partial in TMEM
+// (MH = ceil(Kx/128) halves of 128 lanes x BN columns <= 512 columns); the partials are
+// added in CTA order by a second kernel — deterministic, no atomics.  The tensor core's
+// fp32 accumulator TRUNCATES, which biases a long accumulation chain (1.2e-4 relative over
+// the 16.5 K rows a CTA owns at cfg5): the accumulator is therefore drained every `chunk`
+// steps (1,024 rows) and the chunks are added with round-to-nearest fp32 in the CTA's
+// partial (L2-resident read-modify-write by the epilogue warps; a second TMEM buffer
+// hides the drain when 2·MH·BN <= 512 columns).  3xTF32 like the
+// forward: both tiles are split in place (X = Xh + Xl, G = Gh + Gl) by the splitter warps
+// and D += Xh·Gh + Xl·Gh + Xh·Gl.  HBM-bound: X and G are read exactly once.
+// =====================================================================================
+constexpr int kTRows = 16;                  // rows per stage = two MMA k-steps of 8
+constexpr int kBoxBytes = kTRows * 128;     // one box: 16 rows x 32 floats
+
+// MN-major tf32 operands have ONE legal shared-memory layout (cutlass sm100_common.inl:
+// "for mn-major tf32 operands, SW128_32B is the only available smem layout"): 128-byte rows
+// whose 32-byte chunks are XOR-swizzled with (row % 4) — TMA's SWIZZLE_128B_ATOM_32B, UMMA
+// layout type 1 — in atoms of 4 rows (512 bytes).  32-element chunks along M/N are `lbo`
+// bytes apart, 4-row atoms along K `sbo` bytes apart; one MMA (K = 8) reads two atoms.
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128_32b(uint32_t saddr, uint32_t lbo_bytes) {
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) |
+         (32ull << 32) /* sbo = 512 bytes */ | (1ull << 46) | (1ull << 61);
+}
+
+struct XtgParams {
+  int R, Kx, Ng;
+  int MH;         // 128-row halves of the output (Kx <= 128: 1, else 2)
+  int BN;         // Ng rounded to 16
+  int nbx, nbg;   // boxes per stage: MH*4 of X, ceil(BN/32) of G
+  int stages;
+  int tmem_cols;
+  int nk;         // 16-row steps in total
+  int chunk;      // steps per accumulation chunk (the TMEM accumulator is drained after each)
+  int nbuf;       // accumulator buffers in TMEM: 2 when 2*MH*BN <= 512 columns
+  float* part;    // [grid][MH*128][BN]
+};
+
+template <int PASSES>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_xtg_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapG,
+                const XtgParams P) {
+  extern __shared__ __align__(1024) unsigned char gsm[];
+  __shared__ __align__(8) uint64_t bars[3 * kMaxStages + 4];
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int S = P.stages, BN = P.BN, MH = P.MH, nbuf = P.nbuf;
+  const uint32_t x_bytes = (uint32_t)P.nbx * kBoxBytes, g_bytes = (uint32_t)P.nbg * kBoxBytes;
+  const uint32_t stage_bytes = (PASSES == 3 ? 2 : 1) * (x_bytes + g_bytes);
+  const uint32_t base = (smem_u32(gsm) + 1023u) & ~1023u;
+  auto x_hi = [&](int s) { return base + (uint32_t)s * stage_bytes; };
+  auto x_lo = [&](int s) { return x_hi(s) + x_bytes; };
+  auto g_hi = [&](int s) { return x_hi(s) + (PASSES == 3 ? 2 : 1) * x_bytes; };
+  auto g_lo = [&](int s) { return g_hi(s) + g_bytes; };
+  const uint32_t bar0 = smem_u32(bars);
+  auto full = [&](int s) { return bar0 + 8u * s; };
+  auto ready = [&](int s) { return bar0 + 8u * (kMaxStages + s); };
+  auto empty = [&](int s) { return bar0 + 8u * (2 * kMaxStages + s); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (3 * kMaxStages + b); };
+  auto acc_empty = [&](int b) { return bar0 + 8u * (3 * kMaxStages + 2 + b); };
+
+  // this CTA's contiguous range of 16-row steps (grid <= nk: at least one step each)
+  const int k_begin = (int)((int64_t)P.nk * blockIdx.x / gridDim.x);
+  const int k_end = (int)((int64_t)P.nk * (blockIdx.x + 1) / gridDim.x);
+  const int nsteps = k_end - k_begin;
+  const int nchunks = (nsteps + P.chunk - 1) / P.chunk;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full(s), 1);
+      mbar_init(ready(s), 128);
+      mbar_init(empty(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(acc_full(b), 1);
+      mbar_init(acc_empty(b), 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(&tmem_base_s)),
+                 "r"((uint32_t)P.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_d = tmem_base_s;
+
+  if (warp == 0) {
+    // ===== TMA producer: nbx + nbg boxes of 16 rows x 32 columns per stage =====
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapX) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapG) : "memory");
+      for (int it = 0; it < nsteps; ++it) {
+        const int s = it % S;
+        const uint32_t ph = (uint32_t)(it / S) & 1u;
+        mbar_wait(empty(s), ph ^ 1u);
+        mbar_expect_tx(full(s), x_bytes + g_bytes);
+        const int r0 = (k_begin + it) * kTRows;
+        for (int c = 0; c < P.nbx; ++c)
+          tma_load_2d(x_hi(s) + (uint32_t)c * kBoxBytes, &mapX, full(s), c * 32, r0);
+        for (int c = 0; c < P.nbg; ++c)
+          tma_load_2d(g_hi(s) + (uint32_t)c * kBoxBytes, &mapG, full(s), c * 32, r0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: A = X^T and B = G, both MN-major =====
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) |
+                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+      int it = 0;
+      for (int ch = 0; ch < nchunks; ++ch) {
+        const int buf = ch % nbuf;
+        mbar_wait(acc_empty(buf), ((uint32_t)(ch / nbuf) & 1u) ^ 1u);  // drained by the epilogue
+        tcgen05_fence_after();
+        const uint32_t dcol = tmem_d + (uint32_t)(buf * MH * BN);
+        const int it_end = min(nsteps, (ch + 1) * P.chunk);
+        for (int i0 = it; it < it_end; ++it) {
+          const int s = it % S;
+          const uint32_t ph = (uint32_t)(it / S) & 1u;
+          mbar_wait(PASSES == 3 ? ready(s) : full(s), ph);
+          tcgen05_fence_after();
+#pragma unroll
+          for (int j = 0; j < kTRows / 8; ++j) {   // MMA k-steps of 8 rows = two 4-row atoms, 1024 bytes apart
+            const uint64_t dgh = smem_desc_mn_sw128_32b(g_hi(s) + j * 1024u, kBoxBytes);
+            const uint64_t dgl = smem_desc_mn_sw128_32b(g_lo(s) + j * 1024u, kBoxBytes);
+            for (int h = 0; h < MH; ++h) {
+              const uint32_t hoff = (uint32_t)(h * 4) * kBoxBytes + j * 1024u;
+              const uint64_t dxh = smem_desc_mn_sw128_32b(x_hi(s) + hoff, kBoxBytes);
+              const uint64_t dxl = smem_desc_mn_sw128_32b(x_lo(s) + hoff, kBoxBytes);
+              const uint32_t dc = dcol + (uint32_t)(h * BN);
+              mma_tf32(dc, dxh, dgh, idesc, (it > i0 || j > 0) ? 1u : 0u);
+              if (PASSES == 3) {
+                mma_tf32(dc, dxl, dgh, idesc, 1u);
+                mma_tf32(dc, dxh, dgl, idesc, 1u);
+              }
+            }
+          }
+          tcgen05_commit(empty(s));
+        }
+        tcgen05_commit(acc_full(buf));
+      }
+    }
+  } else if (warp < 6) {
+    // ===== splitter: both tiles, in place (layout-agnostic: element-wise on the raw bytes) =====
+    if (PASSES == 3) {
+      const int t = threadIdx.x - 64;
+      const int nvec = (int)((x_bytes + g_bytes) / 16 / 128);   // float4 per thread: boxes * 1
+      for (int it = 0; it < nsteps; ++it) {
+        const int s = it % S;
+        const uint32_t ph = (uint32_t)(it / S) & 1u;
+        mbar_wait(full(s), ph);
+        const uint32_t xh = x_hi(s);
+        const uint32_t lo_x = x_bytes, lo_g = g_bytes;           // hi -> lo distance per region
+        const uint32_t g_start = (uint32_t)P.nbx * 128u;         // first float4 of the G region
+#pragma unroll 4
+        for (int i = 0; i < nvec; ++i) {
+          const uint32_t v4 = (uint32_t)(t + i * 128);
+          const bool is_g = v4 >= g_start;
+          // hi regions: X at [0, x_bytes), G at [2*x_bytes, 2*x_bytes + g_bytes)
+          const uint32_t src = xh + (is_g ? 2u * x_bytes + (v4 - g_start) * 16u : v4 * 16u);
+          const uint32_t dst = src + (is_g ? lo_g : lo_x);
+          float4 v;
+          asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                       : "r"(src));
+          float4 h, l;
+          h.x = round_tf32(v.x); h.y = round_tf32(v.y);
+          h.z = round_tf32(v.z); h.w = round_tf32(v.w);
+          l.x = round_tf32(v.x - h.x); l.y = round_tf32(v.y - h.y);
+          l.z = round_tf32(v.z - h.z); l.w = round_tf32(v.w - h.w);
+          asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(src), "f"(h.x), "f"(h.y),
+                       "f"(h.z), "f"(h.w)
+                       : "memory");
+          asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "f"(l.x), "f"(l.y),
+                       "f"(l.z), "f"(l.w)
+                       : "memory");
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_arrive(ready(s));
+      }
+    }
+  } else {
+    // ===== epilogue: drain every chunk into this CTA's partial [MH*128, BN] (fp32 adds with
+    // round-to-nearest; every thread owns its addresses, so plain loads and stores) =====
+    const int q = warp & 3;
+    for (int ch = 0; ch < nchunks; ++ch) {
+      const int buf = ch % nbuf;
+      mbar_wait(acc_full(buf), (uint32_t)(ch / nbuf) & 1u);
+      tcgen05_fence_after();
+      for (int h = 0; h < MH; ++h) {
+        float* prow = P.part + ((int64_t)blockIdx.x * (MH * kBM) + h * kBM + q * 32 + lane) * BN;
+        const uint32_t tbase =
+            tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * MH * BN + h * BN);
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t r[32];
+          const int nc = c0 + 32 <= BN ? 32 : 16;
+          if (nc == 32) tmem_ld32(tbase + (uint32_t)c0, r);
+          else tmem_ld16(tbase + (uint32_t)c0, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            if (j < nc) {
+              float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                     __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+              float4* dst = reinterpret_cast<float4*>(prow + c0 + j);
+              if (ch > 0) {
+                const float4 o = *dst;
+                v.x += o.x, v.y += o.y, v.z += o.z, v.w += o.w;
+              }
+              *dst = v;
+            }
+          }
+        }
+      }
+      tcgen05_fence_before();
+      mbar_arrive(acc_empty(buf));  // 128 arrivals: the MMA warp may reuse this buffer
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
+                 "r"((uint32_t)P.tmem_cols)
+                 : "memory");
+  }
+}
+
+// dW[r, c] = sum over the CTAs' partials, in CTA order
+__global__ void __launch_bounds__(256)
+gemm_xtg_reduce_kernel(const float* __restrict__ part, int n_part, int rows_p, int BN, int Kx,
+                       int Ng, float* __restrict__ dW, int64_t ldw) {
+  const int total = Kx * Ng;
+  for (int t = blockIdx.x * 256 + threadIdx.x; t < total; t += gridDim.x * 256) {
+    const int r = t / Ng, c = t - r * Ng;
+    const float* p = part + (int64_t)r * BN + c;
+    float acc = 0.f;
+    for (int b = 0; b < n_part; ++b) acc += p[(int64_t)b * rows_p * BN];
+    dW[(int64_t)r * ldw + c] = acc;
+  }
+}
+
+// 2-D fp32 [rows, cols] (row stride ld), box = 16 rows x 32 columns, SWIZZLE_128B_ATOM_32B
+int make_map_rows16(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld) {
+  return make_map(map, ptr, rows, cols, ld, kTRows, 32, true);
+}
+
+struct XtgPlan {
+  int MH, BN, nbx, nbg, stages, tmem_cols, grid, nk, nbuf;
+  size_t smem, part_floats;
+};
+
+int xtg_plan(int64_t R, int64_t Kx, int64_t Ng, int passes, XtgPlan* pl) {
+  int sms = 148, dev = 0;
+  PYGB_CUDA(cudaGetDevice(&dev));
+  PYGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  pl->MH = Kx <= kBM ? 1 : 2;
+  pl->BN = round_up((int)Ng, 16);
+  pl->nbx = pl->MH * 4;
+  pl->nbg = (pl->BN + 31) / 32;
+  const size_t stage_bytes = (size_t)(passes == 3 ? 2 : 1) * (pl->nbx + pl->nbg) * kBoxBytes;
+  int stages = (int)((226 * 1024 - 1024) / stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  pl->stages = stages;
+  pl->smem = stages * stage_bytes + 1024;
+  pl->nbuf = 2 * pl->MH * pl->BN <= 512 ? 2 : 1;
+  int tc = 32;
+  while (tc < pl->nbuf * pl->MH * pl->BN) tc <<= 1;
+  pl->tmem_cols = tc;
+  pl->nk = (int)ceil_div(R, kTRows);
+  pl->grid = pl->nk < sms ? pl->nk : sms;
+  if (pl->grid < 1) pl->grid = 1;
+  pl->part_floats = (size_t)pl->grid * pl->MH * kBM * pl->BN;
+  return PYGB_OK;
+}
 
 }  // namespace
 }  // namespace pygb
@@ -672,6 +960,75 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
     else PYGB_GEMM_LAUNCH(1, 1, 32);
   }
 #undef PYGB_GEMM_LAUNCH
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+size_t pygb_gemm_xtg_workspace(int64_t R, int64_t Kx, int64_t Ng) {
+  if (R <= 0 || Kx <= 0 || Ng <= 0 || Kx > 256 || Ng > 256) return 256;
+  XtgPlan pl;
+  if (xtg_plan(R, Kx, Ng, 3, &pl) != PYGB_OK) return 0;
+  return align_up(pl.part_floats * sizeof(float), 256) + 256;
+}
+
+int pygb_gemm_xtg(const float* X, int64_t ldx, const float* G, int64_t ldg, int64_t R, int64_t Kx,
+                  int64_t Ng, float* dW, int64_t ldw, int passes, void* ws, size_t ws_bytes,
+                  pygb_stream_t s) {
+  PYGB_REQUIRE(R >= 0 && Kx > 0 && Ng > 0 && R < (1ll << 31) - 256 && ldx >= Kx && ldg >= Ng &&
+                   ldw >= Ng,
+               "pygb_gemm_xtg: bad sizes");
+  PYGB_REQUIRE(passes == 1 || passes == 3, "pygb_gemm_xtg: passes must be 1 (tf32) or 3 (3xtf32)");
+  PYGB_REQUIRE(dW, "pygb_gemm_xtg: null pointer");
+  cudaStream_t st = as_stream(s);
+  if (R == 0) {
+    PYGB_CUDA(cudaMemset2DAsync(dW, (size_t)ldw * 4, 0, (size_t)Ng * 4, (size_t)Kx, st));
+    return PYGB_OK;
+  }
+  PYGB_REQUIRE(X && G && ws, "pygb_gemm_xtg: null pointer");
+  if (Kx > 256 || Ng > 256 || !aligned16(X) || !aligned16(G) || ldx % 4 != 0 || ldg % 4 != 0) {
+    set_error("pygb_gemm_xtg: needs Kx, Ng <= 256 and 16-byte aligned rows of X and G");
+    return PYGB_E_UNSUPPORTED;
+  }
+  XtgPlan pl;
+  int rc = xtg_plan(R, Kx, Ng, passes, &pl);
+  if (rc) return rc;
+  PYGB_REQUIRE(pl.stages >= 2, "pygb_gemm_xtg: tile does not fit shared memory");
+  if (ws_bytes < pygb_gemm_xtg_workspace(R, Kx, Ng)) {
+    set_error("pygb_gemm_xtg: workspace too small");
+    return PYGB_E_WORKSPACE;
+  }
+  XtgParams P;
+  P.R = (int)R;
+  P.Kx = (int)Kx;
+  P.Ng = (int)Ng;
+  P.MH = pl.MH;
+  P.BN = pl.BN;
+  P.nbx = pl.nbx;
+  P.nbg = pl.nbg;
+  P.stages = pl.stages;
+  P.tmem_cols = pl.tmem_cols;
+  P.nk = pl.nk;
+  P.chunk = 1024 / kTRows;
+  P.nbuf = pl.nbuf;
+  P.part = reinterpret_cast<float*>(align_up(reinterpret_cast<size_t>(ws), 256));
+  CUtensorMap mapX, mapG;
+  rc = make_map_rows16(&mapX, X, R, Kx, ldx);
+  if (rc) return rc;
+  rc = make_map_rows16(&mapG, G, R, Ng, ldg);
+  if (rc) return rc;
+  if (passes == 3) {
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_xtg_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(226 * 1024)));
+    gemm_xtg_kernel<3><<<pl.grid, kGemmThreads, pl.smem, st>>>(mapX, mapG, P);
+  } else {
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_xtg_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(226 * 1024)));
+    gemm_xtg_kernel<1><<<pl.grid, kGemmThreads, pl.smem, st>>>(mapX, mapG, P);
+  }
+  PYGB_LAUNCH_CHECK();
+  int64_t blocks = ceil_div(Kx * Ng, 256);
+  gemm_xtg_reduce_kernel<<<(unsigned)blocks, 256, 0, st>>>(P.part, pl.grid, pl.MH * kBM, pl.BN,
+                                                          (int)Kx, (int)Ng, dW, ldw);
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }

@@ -614,6 +614,29 @@ def gemm_xw_raw(x, w, bias=None, passes=None, out=None, relu=False, rows=None):
     return out_full[:, :N] if out_full.size(1) != N else out_full
 
 
+def _xtg_eligible(x, g):
+    return (GEMM_PASSES in (1, 3) and x.is_cuda and x.dim() == 2 and g.dim() == 2
+            and x.dtype == torch.float32 and g.dtype == torch.float32
+            and x.size(0) == g.size(0) and x.size(0) >= 1024
+            and 0 < x.size(1) <= 256 and 0 < g.size(1) <= 256
+            and x.stride(1) == 1 and g.stride(1) == 1 and x.stride(0) % 4 == 0
+            and g.stride(0) % 4 == 0 and x.stride(0) >= x.size(1) and g.stride(0) >= g.size(1)
+            and x.data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0)
+
+
+def gemm_xtg_raw(x, g, passes=None):
+    """``x.t() @ g`` (the weight gradient) by the split-K tcgen05 kernel: both operands are
+    read once, row-major as they are (MN-major tensor-core operands)."""
+    dev = nat.require_cuda(x, g)
+    R, Kx, Ng = x.size(0), x.size(1), g.size(1)
+    out = torch.empty((Kx, Ng), dtype=torch.float32, device=dev)
+    ws_bytes = nat.workspace('pygb_gemm_xtg_workspace', R, Kx, Ng)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    nat.call('pygb_gemm_xtg', dev, nat.ptr(x), x.stride(0), nat.ptr(g), g.stride(0), R, Kx, Ng,
+             nat.ptr(out), Ng, int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
+    return out
+
+
 class _Linear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, bias):
@@ -634,7 +657,10 @@ class _Linear(torch.autograd.Function):
             else:
                 gx = torch.matmul(g, w.t())
         if ctx.needs_input_grad[1]:
-            gw = torch.matmul(x.t(), g)             # reduction over the rows: library split-K GEMM
+            if _xtg_eligible(x, g):                 # dW = x^T g: split-K over the rows on tcgen05
+                gw = gemm_xtg_raw(x, g)
+            else:
+                gw = torch.matmul(x.t(), g)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             gb = g.sum(0)
         return gx, gw, gb

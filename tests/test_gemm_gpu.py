@@ -135,3 +135,73 @@ def test_linear_autograd_and_fallbacks(dev):
     assert _rel(ops.linear(x7, w7), (x7.double() @ w7.double()).cpu()) <= 1e-5
     xb = x.detach().bfloat16()
     assert ops.linear(xb, w.detach().bfloat16()).dtype == torch.bfloat16
+
+
+XTG_SHAPES = [(5000, 100, 256), (70001, 256, 256), (33000, 256, 48), (1024, 16, 16), (9999, 128, 4),
+              (40000, 132, 200), (2500, 4, 256)]
+
+
+@pytest.mark.parametrize('R,Kx,Ng', XTG_SHAPES)
+def test_gemm_xtg_matches_fp64(dev, R, Kx, Ng):
+    """K5t: dW = X^T G (split-K over the rows, MN-major tcgen05 operands) against fp64,
+    run-to-run bit equality, and padded row strides."""
+    from torch_geometric import ops
+    gen = torch.Generator().manual_seed(R + Kx + Ng)
+    x = torch.randn(R, Kx, generator=gen)
+    g = torch.randn(R, Ng, generator=gen)
+    ref = x.double().t() @ g.double()
+    xd, gd = x.to(dev), g.to(dev)
+    assert ops._xtg_eligible(xd, gd)
+    got = ops.gemm_xtg_raw(xd, gd, passes=3)
+    assert got.shape == (Kx, Ng)
+    assert _rel(got, ref) <= 1e-5, _rel(got, ref)
+    assert torch.equal(got, ops.gemm_xtg_raw(xd, gd, passes=3)), 'not deterministic'
+    # plain TF32: 10-bit mantissas
+    assert _rel(ops.gemm_xtg_raw(xd, gd, passes=1), ref) <= 3e-3
+    # views with padded rows (what the padded GEMM / aggregation outputs look like)
+    xp = torch.zeros(R, Kx + 4, device=dev)
+    xp[:, :Kx] = xd
+    gp = torch.zeros(R, Ng + 8, device=dev)
+    gp[:, :Ng] = gd
+    assert torch.equal(ops.gemm_xtg_raw(xp[:, :Kx], gp[:, :Ng], passes=3), got)
+
+
+def test_linear_weight_grad_on_tensor_cores(dev):
+    """_Linear.backward routes dW through K5t when eligible and through the library otherwise."""
+    from torch_geometric import ops, _native as nat
+    gen = torch.Generator().manual_seed(5)
+    x = torch.randn(3000, 100, generator=gen).to(dev).requires_grad_(True)
+    w = (torch.randn(100, 256, generator=gen) / 10).to(dev).requires_grad_(True)
+    nat.event_log = []
+    ops.linear(x, w).square().sum().backward()
+    names = [e[0] for e in nat.event_log]
+    nat.event_log = None
+    assert 'pygb_gemm_xtg' in names
+    xr, wr = (t.detach().double().cpu().requires_grad_(True) for t in (x, w))
+    (xr @ wr).square().sum().backward()
+    assert _rel(w.grad, wr.grad) <= 1e-5
+    assert _rel(x.grad, xr.grad) <= 1e-5
+    # too few rows / too wide: library GEMM
+    assert not ops._xtg_eligible(x[:100], torch.zeros(100, 256, device=dev))
+    assert not ops._xtg_eligible(torch.zeros(2000, 300, device=dev), torch.zeros(2000, 8, device=dev))
+
+
+def test_gemm_xtg_full_size_accuracy(dev):
+    """cfg5's layer-2 weight gradient (2,449,029 rows, 256 x 256): the chunked accumulation keeps
+    the truncating tensor-core accumulator inside the fp32 bar against an fp64 product."""
+    if torch.cuda.get_device_properties(dev).total_memory < 60 * 2 ** 30:
+        pytest.skip('needs a large-memory GPU')
+    from torch_geometric import ops
+    gen = torch.Generator(device=dev).manual_seed(17)
+    R = 2449029
+    x = torch.randn(R, 256, generator=gen, device=dev)
+    g = torch.randn(R, 256, generator=gen, device=dev)
+    got = ops.gemm_xtg_raw(x, g, passes=3)
+    ref = torch.zeros(256, 256, dtype=torch.float64, device=dev)
+    for r0 in range(0, R, 1 << 19):                      # fp64 in slabs: bounded memory
+        ref += x[r0:r0 + (1 << 19)].double().t() @ g[r0:r0 + (1 << 19)].double()
+    err = (got.double() - ref).abs().max().item() / ref.abs().max().item()
+    assert err <= 1e-5, err
+    lib = torch.matmul(x.t(), g)
+    err_lib = (lib.double() - ref).abs().max().item() / ref.abs().max().item()
+    print('xtg rel err %.2e, library fp32 GEMM %.2e' % (err, err_lib))

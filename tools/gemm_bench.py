@@ -37,10 +37,28 @@ def main():
     for name, M, K, N in shapes:
         if args.only and args.only not in name:
             continue
+        if 'xtg' in args.kinds.split(',') and K <= 256 and N <= 256:
+            # dW = x^T g (K5t) against the library's fp32 GEMM
+            x = torch.randn(M, K, device=dev)
+            # gradients reach the GEMM with rows padded to 16 bytes (outputs of K1 / K5)
+            g = torch.randn(M, (N + 3) // 4 * 4, device=dev)[:, :N]
+            ref = torch.matmul(x.t(), g)
+            for kind, fn in (('lib x^T g', lambda: torch.matmul(x.t(), g)),
+                             ('xtg 3xtf32', lambda: ops.gemm_xtg_raw(x, g, passes=3)),
+                             ('xtg tf32', lambda: ops.gemm_xtg_raw(x, g, passes=1))):
+                ms = timeit(fn)
+                err = (fn() - ref).abs().max().item() / ref.abs().max().item()
+                print(json.dumps({'shape': name + ' dW', 'R': M, 'Kx': K, 'Ng': N, 'kernel': kind,
+                                  'ms': round(ms, 4), 'TFLOPs': round(2.0 * M * K * N / ms / 1e9, 1),
+                                  'GBps': round(4.0 * M * (K + N) / ms / 1e6, 1),
+                                  'rel_vs_lib': float('%.3e' % err)}), flush=True)
+            del x, g, ref
         x = torch.randn(M, K, device=dev)
         w = torch.randn(K, N, device=dev) / K ** 0.5
         ref = None
         for kind in args.kinds.split(','):
+            if kind == 'xtg':
+                continue
             if kind == 'lib':
                 fn = lambda: torch.matmul(x, w)
             else:
