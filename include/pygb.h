@@ -314,6 +314,17 @@ int pygb_gat_backward_stream(int mode, const float* row_feat, int64_t ld_row,
                              int32_t Ts, int64_t n_sub, float* d_feat, int64_t ldd, float* d_a,
                              void* ws, size_t ws_bytes, pygb_stream_t s);
 
+/* ---- k-NN graph (the step before EdgeConv's propagate) ------------------------ */
+
+/* nbr[q, r] = index of the r-th nearest point of q inside q's example (squared Euclidean
+ * distance in fp32, ties to the lower index; -1 when the example has fewer candidates) —
+ * `torch_cluster.knn_graph` of the reference (README.md:149-150, examples/pointnet++.py:39-41;
+ * DynamicEdgeConv).  x [n, D] fp32 (row stride ldx), batch int64 [n] sorted, ptr int64 [B+1]
+ * the first point of every example.  loop != 0 keeps q itself as a candidate.
+ * k <= 64, D <= 128 (else PYGB_E_UNSUPPORTED). */
+int pygb_knn_graph(const float* x, int64_t ldx, int64_t n, int D, const int64_t* batch,
+                   const int64_t* ptr, int k, int loop, int32_t* nbr, pygb_stream_t s);
+
 /* ---- K5: dense node-feature transform on the tensor cores ------------------ */
 
 /* C[M,N] = A[M,K] . W[K,N] (+ bias[N]), fp32 in / fp32 out — the

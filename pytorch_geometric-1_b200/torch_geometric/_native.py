@@ -71,6 +71,7 @@ SIGNATURES = {
     'pygb_gat_alpha': (_I, [_P, _P, _I, _F, _P, _P, _P, _L, _P, _P, _P, _P]),
     'pygb_gemm_weight_workspace': (_Z, [_L, _L]),
     'pygb_gemm_xw': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _P, _Z, _P]),
+    'pygb_knn_graph': (_I, [_P, _L, _L, _I, _P, _P, _I, _I, _P, _P]),
     'pygb_gemm_xtg_workspace': (_Z, [_L, _L, _L]),
     'pygb_gemm_xtg': (_I, [_P, _L, _P, _L, _L, _L, _L, _P, _L, _I, _P, _Z, _P]),
     'pygb_gat_edge_grad': (_I, [_P, _L, _P, _P, _I, _I, _F, _P, _P, _P, _L, _P, _L, _P, _P, _L,

@@ -194,3 +194,58 @@ def test_topk_pooling(dev, ratio):
     (rr * gw).sum().backward()
     assert_close(xg.grad, xr.grad, 1e-5, 'grad x')
     assert_close(pool.weight.grad.view(-1), w.grad, 1e-5, 'grad weight')
+
+
+@pytest.mark.parametrize('D,k,loop', [(3, 20, False), (3, 6, True), (16, 8, False), (64, 20, False)])
+def test_knn_graph_kernel(dev, D, k, loop):
+    """pygb_knn_graph (csrc/knn.cu) against an fp64 brute force: edges grouped by centre,
+    neighbours in ascending distance, the k-th distance exact to fp32 rounding, examples of
+    different sizes (one smaller than k)."""
+    from torch_geometric.nn import knn_graph
+    gen = torch.Generator().manual_seed(D + k)
+    sizes = [300, 5, 1024, 130, 77]
+    n = sum(sizes)
+    x = torch.rand(n, D, generator=gen) * 2 - 1
+    batch = torch.cat([torch.full((s,), i) for i, s in enumerate(sizes)]).long()
+    ei = knn_graph(x.to(dev), k, batch.to(dev), loop=loop).cpu()
+    assert ei.dtype == torch.long and torch.equal(batch[ei[0]], batch[ei[1]])
+    assert bool((ei[1][1:] >= ei[1][:-1]).all()), 'edges not grouped by centre'
+    xd = x.double()
+    start = 0
+    e = 0
+    for s in sizes:
+        d = torch.cdist(xd[start:start + s], xd[start:start + s]) ** 2
+        if not loop:
+            d.fill_diagonal_(float('inf'))
+        kk = min(k, s - (0 if loop else 1))
+        ref_d = d.topk(kk, dim=1, largest=False)[0]
+        for i in range(s):
+            assert bool((ei[1][e:e + kk] == start + i).all())
+            got = d[i, ei[0][e:e + kk] - start]
+            assert bool((got[1:] >= got[:-1] - 1e-6).all()), 'neighbours not in ascending distance'
+            assert torch.allclose(got, ref_d[i], rtol=1e-5, atol=1e-7)
+            if not loop:
+                assert bool((ei[0][e:e + kk] != start + i).all())
+            e += kk
+        start += s
+    assert e == ei.size(1)
+    # flow and the default batch
+    assert torch.equal(knn_graph(x.to(dev), k, batch.to(dev), loop=loop, flow='target_to_source').cpu(),
+                       ei.flip(0))
+    one = knn_graph(x[:300].to(dev), 4).cpu()
+    assert one.shape == (2, 1200)
+
+
+def test_dynamic_edge_conv_uses_knn_kernel(dev):
+    from torch_geometric.nn import DynamicEdgeConv
+    from torch_geometric import _native as nat
+    torch.manual_seed(0)
+    mlp = torch.nn.Sequential(torch.nn.Linear(6, 16), torch.nn.ReLU(), torch.nn.Linear(16, 16))
+    conv = DynamicEdgeConv(mlp, k=6).to(dev)
+    pos = torch.rand(512, 3, device=dev)
+    batch = torch.arange(4, device=dev).repeat_interleave(128)
+    nat.event_log = []
+    out = conv(pos, batch)
+    names = [e[0] for e in nat.event_log]
+    nat.event_log = None
+    assert 'pygb_knn_graph' in names and out.shape == (512, 16)
