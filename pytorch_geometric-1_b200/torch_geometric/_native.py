@@ -148,21 +148,35 @@ def ptr(t):
     return None if t is None else t.data_ptr()
 
 
+def _raw_stream(idx):
+    """cudaStream_t of the current stream of device ``idx`` without building a Stream object."""
+    try:
+        return torch._C._cuda_getCurrentRawStream(idx)
+    except AttributeError:  # pragma: no cover - older/newer torch builds
+        return torch.cuda.current_stream(idx).cuda_stream
+
+
 def call(name, device, *args):
     """Invoke ``name(*args, stream)`` on ``device``'s current stream."""
     global launches
     lib = load()
-    with torch.cuda.device(device):
-        cur = torch.cuda.current_stream()
-        if event_log is not None:
-            e0 = torch.cuda.Event(enable_timing=True)
-            e1 = torch.cuda.Event(enable_timing=True)
-            e0.record(cur)
-            rc = getattr(lib, name)(*args, cur.cuda_stream)
-            e1.record(cur)
-            event_log.append((name, args, e0, e1))
-        else:
-            rc = getattr(lib, name)(*args, cur.cuda_stream)
+    fn = getattr(lib, name)
+    idx = device.index
+    if event_log is None and (idx is None or idx == torch.cuda.current_device()):
+        # fast path (small graphs are launch-latency bound): no device guard, no Stream object
+        rc = fn(*args, _raw_stream(torch.cuda.current_device() if idx is None else idx))
+    else:
+        with torch.cuda.device(device):
+            cur = torch.cuda.current_stream()
+            if event_log is not None:
+                e0 = torch.cuda.Event(enable_timing=True)
+                e1 = torch.cuda.Event(enable_timing=True)
+                e0.record(cur)
+                rc = fn(*args, cur.cuda_stream)
+                e1.record(cur)
+                event_log.append((name, args, e0, e1))
+            else:
+                rc = fn(*args, cur.cuda_stream)
     launches += 1
     if rc != 0:
         raise NativeError('{} failed ({}): {}'.format(name, rc, lib.pygb_last_error().decode()))
@@ -176,8 +190,19 @@ def call_host(name, *args):
         raise NativeError('{} failed ({}): {}'.format(name, rc, lib.pygb_last_error().decode()))
 
 
+_ws_cache = {}
+
+
 def workspace(name, *args):
-    return int(getattr(load(), name)(*args))
+    """Workspace size query (pure functions of their arguments: memoised)."""
+    key = (name,) + args
+    hit = _ws_cache.get(key)
+    if hit is None:
+        hit = int(getattr(load(), name)(*args))
+        if len(_ws_cache) > 4096:
+            _ws_cache.clear()
+        _ws_cache[key] = hit
+    return hit
 
 
 def dtype_code(t):
