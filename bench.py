@@ -439,7 +439,7 @@ def run_b200(args):
         for _ in range(2):
             e2e_step()
         barrier()
-        k = max(3, min(args.steps, 10))
+        k = max(3, min(args.steps, 50))   # same K as the device-timed region (fill + drain included)
         ev0.record()
         for _ in range(k):
             e2e_step()

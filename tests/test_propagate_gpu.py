@@ -189,7 +189,7 @@ def test_gcn_bf16(dev):
 
 
 @pytest.mark.parametrize('H,C,concat', [(8, 8, True), (1, 16, True), (4, 7, False), (6, 121, False),
-                                        (2, 64, True)])
+                                        (2, 64, True), (8, 8, False), (4, 128, True), (3, 12, True)])
 def test_gat_conv_forward_backward(dev, H, C, concat):
     from torch_geometric.nn import GATConv
     n, E, fin = 900, 12000, 40
