@@ -73,3 +73,4 @@ def test_knn_graph_matches_brute_force():
         assert torch.equal(batch[ei[0]], batch[ei[1]])
     flipped = knn_graph(x, 4, batch, flow='target_to_source')
     assert torch.equal(flipped.flip(0), knn_graph(x, 4, batch))
+    assert knn_graph(torch.zeros(0, 3), 4).shape == (2, 0)
