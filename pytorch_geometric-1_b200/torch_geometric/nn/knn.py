@@ -39,9 +39,9 @@ def _knn_cuda(x, k, batch, loop):
 def knn_graph(x, k, batch=None, loop=False, flow='source_to_target'):
     assert flow in ['source_to_target', 'target_to_source']
     n = x.size(0)
-    x = x.view(n, -1)
     if n == 0:
         return torch.empty((2, 0), dtype=torch.long, device=x.device)
+    x = x.view(n, -1)
     if batch is None:
         batch = x.new_zeros(n, dtype=torch.long)
     if x.is_cuda and n > 0 and 0 < k <= 64 and x.size(1) <= 128:
