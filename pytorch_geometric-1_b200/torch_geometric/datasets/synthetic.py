@@ -6,7 +6,6 @@ seed.  All generators run on any torch device (the large ones are meant to be
 generated directly on the GPU) and use only torch ops, so the same seed gives
 the same graph on the same device type.
 """
-import math
 
 import torch
 

@@ -84,7 +84,6 @@ def test_stream_single_giant_row_and_all_empty(dev, ops_mod):
 def test_stream_gat_matches_oracle_and_v1(dev, ops_mod, H, C, T):
     """K2 v2 (online softmax, pieces merged across sub-items) vs the oracle GATConv and
     the two-pass kernel; hub rows of ~1000 edges and empty rows."""
-    import copy
     from torch_geometric.nn import GATConv
     ops = ops_mod
     n, E, fin = 600, 9000, 20

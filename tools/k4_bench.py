@@ -53,7 +53,6 @@ def k4_bytes(E, Ep, N):
 def cfg5(dev, iters):
     from torch_geometric.datasets import synthetic
     from torch_geometric.nn import GCNConv
-    from torch_geometric.graph import adj_for
     data = synthetic.products_like(seed=4, device=dev)
     ei, N = data.edge_index, data.x.size(0)
     x = torch.randn(N, 48, device=dev)
