@@ -906,6 +906,9 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
   // Tile shape.  256 x BN x 16 shares every W stage between two 128-row halves: worth it when
   // W traffic dominates the stage (3 passes, wide BN) and there are enough tiles for every SM.
   int mh = 1, bk = kBK;
+  // a k-step of 16 wastes less of the last step when K is just above a multiple of 32
+  // (K = 100: 112 instead of 128 columns of MMAs and W traffic; profiles/r01_k5_tiles.md)
+  if (round_up((int)K, 16) < round_up((int)K, 32) && K > 32) bk = 16;
   if (const char* e = getenv("PYGB_GEMM_TILE")) {     // tuning / tests: "128x32", "128x16", "256x16"
     int tm = 0, tk = 0;
     if (sscanf(e, "%dx%d", &tm, &tk) == 2 && (tm == 128 || tm == 256) && (tk == 16 || tk == 32) &&
