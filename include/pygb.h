@@ -113,6 +113,13 @@ int pygb_weighted_degree(const float* w, const int32_t* rowptr, const int32_t* p
 int pygb_gcn_norm(const int64_t* edge_index, const float* w, int64_t E, int64_t N,
                   const float* deg, float* norm, pygb_stream_t s);
 
+/* The unit-weight normalisation in the slot order of a sorted graph: out[p] =
+ * deg[col[p]]^-1/2 * deg[i]^-1/2 for slot p of row i — bit-identical to
+ * pygb_permute_f32(pygb_gcn_norm(...), perm) when every edge weight is 1, without the
+ * random gather (first call of GCNConv(cached=True), examples/gcn.py:18-19). */
+int pygb_gcn_norm_csr(const int32_t* rowptr, const int32_t* col, const float* deg,
+                      int64_t n_rows, float* out, pygb_stream_t s);
+
 /* ---- K1: segmented gather-reduce (aggr = add | mean) ---------------------- */
 
 /* out[i, :] = reduce_{p in [rowptr[i], rowptr[i+1])} w_p * x[idx[p], :]

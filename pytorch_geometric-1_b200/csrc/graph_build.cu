@@ -465,6 +465,22 @@ gcn_norm_kernel(const int64_t* __restrict__ row, const int64_t* __restrict__ col
   }
 }
 
+// The same product, written directly in the slot order of a sorted graph: slot p of row i
+// has the end points (i, col[p]); one warp per row.  Bit-identical to norm[perm[p]] for unit
+// weights (fmul is commutative), without the random 4-byte gather.
+__global__ void __launch_bounds__(kThreads)
+gcn_norm_csr_kernel(const int* __restrict__ rowptr, const int* __restrict__ col,
+                    const float* __restrict__ deg, int64_t n_rows, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t nw = (int64_t)gridDim.x * kWarps;
+  for (int64_t r = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5); r < n_rows; r += nw) {
+    const int b = rowptr[r], e = rowptr[r + 1];
+    if (b == e) continue;
+    const float di = inv_sqrt_deg(deg[r]);
+    for (int p = b + lane; p < e; p += 32) out[p] = __fmul_rn(inv_sqrt_deg(deg[col[p]]), di);
+  }
+}
+
 }  // namespace
 }  // namespace pygb
 
@@ -688,6 +704,19 @@ int pygb_gcn_norm(const int64_t* edge_index, const float* w, int64_t E, int64_t 
   if (E == 0) return PYGB_OK;
   gcn_norm_kernel<<<grid_for(E), kThreads, 0, as_stream(s)>>>(edge_index, edge_index + E, w, E,
                                                              deg, norm);
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+int pygb_gcn_norm_csr(const int32_t* rowptr, const int32_t* col, const float* deg,
+                      int64_t n_rows, float* out, pygb_stream_t s) {
+  PYGB_REQUIRE(n_rows >= 0, "pygb_gcn_norm_csr: bad arguments");
+  if (n_rows == 0) return PYGB_OK;
+  PYGB_REQUIRE(rowptr && col && deg && out, "pygb_gcn_norm_csr: null pointer");
+  int64_t blocks = ceil_div(n_rows, kWarps);  // one row per warp: latency hidden by occupancy
+  if (blocks > (1 << 30)) blocks = 1 << 30;
+  gcn_norm_csr_kernel<<<(unsigned)blocks, kThreads, 0, as_stream(s)>>>(rowptr, col, deg, n_rows,
+                                                                      out);
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }

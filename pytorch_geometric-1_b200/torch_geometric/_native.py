@@ -34,6 +34,7 @@ SIGNATURES = {
     'pygb_degree': (_I, [_P, _L, _L, _I, _P, _P]),
     'pygb_weighted_degree': (_I, [_P, _P, _P, _L, _P, _P]),
     'pygb_gcn_norm': (_I, [_P, _P, _L, _L, _P, _P, _P]),
+    'pygb_gcn_norm_csr': (_I, [_P, _P, _P, _L, _P, _P]),
     'pygb_seg_gather_reduce': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
     'pygb_seg_plan': (_I, [_L, _P, _P]),
     'pygb_seg_tables_workspace': (_Z, [_L]),

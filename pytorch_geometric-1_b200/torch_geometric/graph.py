@@ -226,8 +226,16 @@ class Adj(object):
             return hit[0]
         csr = self.dst if which == 'dst' else self.src
         out = torch.empty_like(w)
-        nat.call('pygb_permute_f32', w.device, nat.ptr(w), nat.ptr(csr.perm), w.numel(),
-                 nat.ptr(out))
+        tag = getattr(w, '_pygb_unit_deg', None)
+        deg = tag[0] if tag is not None and tag[1] == w._version else None
+        if (deg is not None and w.dtype == torch.float32 and w.numel() == csr.E
+                and deg.numel() == csr.n_rows == csr.n_cols and csr.col is not None):
+            # GCNConv.norm with unit weights: D^-1/2 A D^-1/2 straight in slot order
+            nat.call('pygb_gcn_norm_csr', w.device, nat.ptr(csr.rowptr), nat.ptr(csr.col),
+                     nat.ptr(deg), csr.n_rows, nat.ptr(out))
+        else:
+            nat.call('pygb_permute_f32', w.device, nat.ptr(w), nat.ptr(csr.perm), w.numel(),
+                     nat.ptr(out))
         if len(self._wcache) > 4:
             self._wcache.clear()
         self._wcache[key] = (out, w)

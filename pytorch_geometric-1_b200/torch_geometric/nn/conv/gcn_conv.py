@@ -73,6 +73,10 @@ class GCNConv(MessagePassing):
                  nat.ptr(norm))
         if dtype is not None and dtype != torch.float32:
             norm = norm.to(dtype)
+        elif unit:
+            # unit weights: the sorted-order copy of norm can be rebuilt from the degrees
+            # (graph.Adj.permuted) instead of gathered through the permutation
+            norm._pygb_unit_deg = (deg, norm._version)
         return edge_index, norm
 
     def _aggregate_first(self, x):

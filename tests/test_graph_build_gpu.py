@@ -143,3 +143,31 @@ def test_weighted_degree_bit_exact(dev):
     nat.call('pygb_weighted_degree', dev, nat.ptr(wd), nat.ptr(csr.rowptr), nat.ptr(csr.perm), n,
              nat.ptr(deg))
     assert torch.equal(deg.cpu(), ref)
+
+
+def test_gcn_norm_in_slot_order_is_bit_identical(dev):
+    """Adj.permuted rebuilds the unit-weight GCN norm from the degrees in slot order
+    (pygb_gcn_norm_csr) — the same bits as gathering norm through the permutation, for both
+    sorted graphs; a norm that was modified in place falls back to the gather."""
+    from torch_geometric.nn import GCNConv
+    from torch_geometric.graph import Adj
+    from torch_geometric import _native as nat
+    ei = skewed_graph(900, 12000, 21).to(dev)
+    ei2, norm = GCNConv.norm(ei, 900)
+    assert hasattr(norm, '_pygb_unit_deg')
+    adj = Adj(ei2, 1, (900, 900))
+    nat.event_log = []
+    got_d, got_s = adj.permuted(norm, 'dst'), adj.permuted(norm, 'src')
+    names = [e[0] for e in nat.event_log]
+    nat.event_log = None
+    assert names.count('pygb_gcn_norm_csr') == 2 and 'pygb_permute_f32' not in names
+    assert torch.equal(got_d, norm[adj.dst.perm.long()])
+    assert torch.equal(got_s, norm[adj.src.perm.long()])
+    norm.mul_(2.0)                                   # stale tag: version changed
+    adj2 = Adj(ei2, 1, (900, 900))
+    assert torch.equal(adj2.permuted(norm, 'dst'), norm[adj2.dst.perm.long()])
+    # weighted / improved norms carry no tag
+    _, nw = GCNConv.norm(ei, 900, torch.rand(ei.size(1), device=dev))
+    assert not hasattr(nw, '_pygb_unit_deg')
+    _, ni = GCNConv.norm(ei, 900, None, True)
+    assert not hasattr(ni, '_pygb_unit_deg')
