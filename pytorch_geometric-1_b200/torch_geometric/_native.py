@@ -92,6 +92,14 @@ class NativeError(RuntimeError):
     pass
 
 
+if os.environ.get('PYGB_LOG_NATIVE_CALLS', '0') not in ('', '0'):
+    import atexit
+
+    @atexit.register
+    def _report_calls():          # evidence that a user script ran on libpygb.so (tests)
+        print('[pygb] native calls: {}'.format(launches), flush=True)
+
+
 def load():
     """Load libpygb.so (once).  Raises if it has not been built."""
     global _lib

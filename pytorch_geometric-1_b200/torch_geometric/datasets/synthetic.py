@@ -151,6 +151,54 @@ def products_like(seed=4, device='cpu', num_nodes=2449029, num_pairs=31000000, n
     return Data(x=x, edge_index=ei, y=y)
 
 
+def graph_collection(count, mean_nodes, mean_pairs, num_labels, num_attrs, num_classes, seed,
+                     multilabel=False):
+    """``count`` small graphs (TUDataset- / PPI-shaped): node count ~ Poisson-like around
+    ``mean_nodes``, ``mean_pairs`` undirected pairs, x = [attrs | one-hot label]."""
+    gen = _gen(seed, torch.device('cpu'))
+    out = []
+    for gi in range(count):
+        n = max(3, int(torch.normal(float(mean_nodes), float(mean_nodes) ** 0.5 * 1.5,
+                                    (1,), generator=gen).item()))
+        pairs = max(2, int(n * mean_pairs / mean_nodes))
+        pairs = min(pairs, n * (n - 1) // 2)
+        a = torch.randint(0, n, (pairs,), generator=gen)
+        b = (a + 1 + torch.randint(0, n - 1, (pairs,), generator=gen)) % n
+        ei = torch.stack([torch.cat([a, b]), torch.cat([b, a])])
+        cols = []
+        if num_attrs:
+            cols.append(torch.randn(n, num_attrs, generator=gen))
+        if num_labels:
+            lab = torch.randint(0, num_labels, (n,), generator=gen)
+            cols.append(torch.nn.functional.one_hot(lab, num_labels).float())
+        x = torch.cat(cols, dim=1)
+        if multilabel:
+            y = (torch.rand(n, num_classes, generator=gen) < 0.3).float()
+        else:
+            y = torch.randint(0, num_classes, (1,), generator=gen)
+        out.append(Data(x=x, edge_index=ei, y=y))
+    return out
+
+
+def superpixel_collection(count, nodes, k, seed):
+    """MNISTSuperpixels-shaped graphs: ``nodes`` points in [0, 28)^2 with one intensity
+    feature, symmetric k-nearest-neighbour edges, ``pos`` set (for ``T.Cartesian``)."""
+    gen = _gen(seed, torch.device('cpu'))
+    out = []
+    for gi in range(count):
+        pos = torch.rand(nodes, 2, generator=gen) * 28
+        d = torch.cdist(pos, pos)
+        d.fill_diagonal_(float('inf'))
+        nbr = d.topk(k, dim=1, largest=False)[1]
+        src = torch.arange(nodes).view(-1, 1).expand(-1, k).reshape(-1)
+        code = torch.unique(torch.cat([src * nodes + nbr.reshape(-1),
+                                       nbr.reshape(-1) * nodes + src]))
+        ei = torch.stack([code // nodes, code % nodes])
+        out.append(Data(x=torch.rand(nodes, 1, generator=gen), edge_index=ei, pos=pos,
+                        y=torch.randint(0, 10, (1,), generator=gen)))
+    return out
+
+
 def knn_clouds(num_clouds=32, points=1024, k=20, seed=3, device='cpu'):
     """cfg 4: ``num_clouds`` clouds of U(-1,1)^3 points with an exact k-NN graph
     inside each cloud; edges are (neighbour -> centre), grouped by centre."""

@@ -6,7 +6,7 @@ from ... import ops
 from ...graph import adj_for
 from ...utils import add_self_loops, remove_self_loops, softmax
 from ..inits import glorot, zeros
-from .message_passing import MessagePassing
+from .message_passing import MessagePassing, Updated
 
 
 class GATConv(MessagePassing):
@@ -94,8 +94,11 @@ class GATConv(MessagePassing):
         fuse_bias = self.bias is not None and self.concat
         out = ops.gat_propagate(x_src, x_dst, self.att, self.bias if fuse_bias else None, adj,
                                 self.heads, self.out_channels, self.negative_slope)
-        self._bias_fused = fuse_bias
-        return out.view(-1, self.heads, self.out_channels)
+        # update(): concat -> [N, H*C] with the bias added by the kernel; else head mean + bias
+        if self.concat:
+            return Updated(out.view(-1, self.heads * self.out_channels))
+        out = out.view(-1, self.heads, self.out_channels).mean(dim=1)
+        return Updated(out + self.bias if self.bias is not None else out)
 
     def message(self, edge_index_i, x_i, x_j, size_i):
         # generic route (dropout on alpha, or user subclasses)
@@ -119,9 +122,6 @@ class GATConv(MessagePassing):
         else:
             aggr_out = aggr_out.mean(dim=1)
 
-        if getattr(self, '_bias_fused', False):
-            self._bias_fused = False
-            return aggr_out
         if self.bias is not None:
             aggr_out = aggr_out + self.bias
         return aggr_out
@@ -129,7 +129,6 @@ class GATConv(MessagePassing):
     def __getstate__(self):
         state = self.__dict__.copy()
         state.pop('_loop_cache', None)
-        state.pop('_bias_fused', None)
         return state
 
     def __repr__(self):

@@ -6,7 +6,7 @@ from ... import ops
 from ...graph import adj_for, build_csr
 from ...utils import add_remaining_self_loops
 from ..inits import glorot, zeros
-from .message_passing import MessagePassing
+from .message_passing import MessagePassing, Updated
 
 
 class GCNConv(MessagePassing):
@@ -121,11 +121,11 @@ class GCNConv(MessagePassing):
         edge_index, norm = self.cached_result
 
         if agg_first:
-            self._defer_bias = True
-            try:
-                h = self.propagate(edge_index, x=x, norm=norm)
-            finally:
-                self._defer_bias = False
+            # stock message/update (checked by _aggregate_first): the fused aggregation is
+            # called directly, the bias follows the transform — no per-call state on self
+            i = 0 if self.flow == 'target_to_source' else 1
+            n = x.size(0)
+            h = ops.gather_reduce(x, adj_for(edge_index, i, (n, n)), norm, 'sum', None)
             return ops.linear(h, self.weight, self.bias)
         return self.propagate(edge_index, x=x, norm=norm)
 
@@ -138,20 +138,13 @@ class GCNConv(MessagePassing):
         if not torch.is_tensor(x) or x.dtype not in (torch.float32, torch.bfloat16):
             return NotImplemented
         adj = adj_for(edge_index, i, size)
-        bias = None if getattr(self, '_defer_bias', False) else self.bias
-        out = ops.gather_reduce(x, adj, norm, 'sum', bias)
-        self._bias_fused = bias is not None
-        return out
+        # update() (= + bias) runs in the kernel epilogue
+        return Updated(ops.gather_reduce(x, adj, norm, 'sum', self.bias))
 
     def message(self, x_j, norm):
         return norm.view(-1, 1) * x_j if norm is not None else x_j
 
     def update(self, aggr_out):
-        if getattr(self, '_bias_fused', False):
-            self._bias_fused = False  # the fused kernel's epilogue already added it
-            return aggr_out
-        if getattr(self, '_defer_bias', False):
-            return aggr_out  # (A X) W + b: the bias follows the transform in forward()
         if self.bias is not None:
             aggr_out = aggr_out + self.bias
         return aggr_out
@@ -161,8 +154,6 @@ class GCNConv(MessagePassing):
         state = self.__dict__.copy()
         state['cached_result'] = None
         state['cached_num_edges'] = None
-        state.pop('_bias_fused', None)
-        state.pop('_defer_bias', None)
         return state
 
     def __repr__(self):

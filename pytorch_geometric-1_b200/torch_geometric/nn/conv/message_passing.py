@@ -29,6 +29,16 @@ __size_error_msg__ = ('All tensors which should get mapped to the same source '
                       'or target nodes must be of same size in dimension 0.')
 
 
+class Updated(object):
+    """Return type of a fused route that has already applied ``update()`` (bias fused
+    into the kernel epilogue): ``propagate`` returns ``value`` as is.  Call-local, so
+    conv modules keep no per-call state and stay re-entrant under ``parallel_apply``."""
+    __slots__ = ('value',)
+
+    def __init__(self, value):
+        self.value = value
+
+
 class MessagePassing(torch.nn.Module):
     def __init__(self, aggr='add', flow='source_to_target', node_dim=0):
         super(MessagePassing, self).__init__()
@@ -49,7 +59,8 @@ class MessagePassing(torch.nn.Module):
 
     # -- fused routes ------------------------------------------------------
     def _fused_propagate(self, edge_index, size, i, kwargs):
-        """Return the aggregated (pre-``update``) tensor or ``NotImplemented``."""
+        """Return the aggregated (pre-``update``) tensor, ``Updated(final)`` when the
+        route also covered ``update()``, or ``NotImplemented``."""
         cls = type(self)
         if cls.message is not MessagePassing.message or self.node_dim != 0:
             return NotImplemented
@@ -121,6 +132,9 @@ class MessagePassing(torch.nn.Module):
         out = NotImplemented
         if size[0] is not None and size[1] is not None:
             out = self._fused_propagate(edge_index, size, i, kwargs)
+
+        if isinstance(out, Updated):
+            return out.value
 
         if out is NotImplemented:
             message_args = []

@@ -20,6 +20,8 @@ class _WeightedSum(MessagePassing):
         cls = type(self)
         if cls.message is not _WeightedSum.message or self.node_dim != 0:
             return NotImplemented
+        if self.aggr not in ('add', 'mean'):
+            return NotImplemented          # weighted max: generic route (scatter_max kernel)
         x, norm = kwargs.get('x'), kwargs.get('norm')
         if isinstance(x, (tuple, list)):
             x = x[1 - i]
@@ -100,6 +102,8 @@ class GraphConv(_WeightedSum):
     def _fused_propagate(self, edge_index, size, i, kwargs):
         if type(self).message is not GraphConv.message or self.node_dim != 0:
             return NotImplemented
+        if self.aggr not in ('add', 'mean'):
+            return NotImplemented          # aggr='max': generic route (scatter_max kernel)
         h, norm = kwargs.get('h'), kwargs.get('norm')
         if not torch.is_tensor(h) or h.dtype not in (torch.float32, torch.bfloat16):
             return NotImplemented
