@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define PYGB_ABI_VERSION 3
+#define PYGB_ABI_VERSION 4
 
 enum { PYGB_OK = 0, PYGB_E_ARG = -1, PYGB_E_CUDA = -2, PYGB_E_WORKSPACE = -3,
        PYGB_E_UNSUPPORTED = -4 };
@@ -63,6 +63,12 @@ int pygb_check_device(int* sm_count, int* cc_major, int* cc_minor);
  * add_remaining_self_loops (A.2; ref site examples/qm9_nn_conv.py:11). */
 int pygb_count_self_loops(const int64_t* edge_index, int64_t E, int64_t* d_count,
                           pygb_stream_t s);
+
+/* One pass over edge_index: d_out[0] = edges with row == col, d_out[1] = edges with an
+ * id outside [0, N) (device int64[2]).  The count the self-loop utilities need plus the
+ * range check GCNConv.norm owes its callers, behind a single device->host read. */
+int pygb_scan_edge_index(const int64_t* edge_index, int64_t E, int64_t N, int64_t* d_out,
+                         pygb_stream_t s);
 
 /* Self-loop handling (A.2).  `n_loops` is the value of pygb_count_self_loops
  * (ignored for PYGB_LOOPS_ADD).  E' = E - n_loops (REMOVE), E + N (ADD),
@@ -202,6 +208,16 @@ int pygb_seg_gather_reduce_heads(int dtype, const void* x, int64_t ldx, int H, i
 int pygb_gather_rows(int dtype, const void* x, int64_t ldx, int64_t F,
                      const int64_t* index, int64_t E, void* out, int64_t ldo,
                      pygb_stream_t s);
+
+/* out[perm[p]] = <g[row(p), :], x[col[p], :]> for every slot p of the sorted
+ * graph (fp32, original edge order): the gradient of the fused weighted
+ * aggregation with respect to the edge weight (autograd of GCNConv.message
+ * `norm.view(-1, 1) * x_j`, A.9; ref site examples/gcn.py:25 with edge weights,
+ * SURVEY 7.3 hard part 4).  No [E, F] temporary. */
+int pygb_edge_dot(int dtype, const void* g, int64_t ldg, const void* x, int64_t ldx,
+                  int64_t F, const int32_t* rowptr, const int32_t* col,
+                  const int32_t* perm, int64_t n_rows, int64_t E, float* out,
+                  pygb_stream_t s);
 
 /* ---- K3: segmented max with argmax (aggr = max) --------------------------- */
 
@@ -353,6 +369,14 @@ int pygb_gemm_xw(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane,
                  int64_t K, const float* W, int64_t ldw, int64_t N, const float* bias,
                  int relu, float* C, int64_t ldc, int passes, void* ws, size_t ws_bytes,
                  pygb_stream_t s);
+
+/* The same transform for bf16 operands and a bf16 result (north_star's 1e-2 bf16 mode;
+ * SURVEY 8b `pygb_gemm_tcgen05(in_dtype tf32|bf16)`): tcgen05.mma kind::f16 with fp32
+ * accumulation in TMEM, one pass, k-steps of 64 (or 32) elements.  A must be 16-byte
+ * aligned with lda % 8 == 0; bias stays fp32; `ws` as above. */
+int pygb_gemm_xw_bf16(const void* A, int64_t lda, int64_t M, int64_t K, const void* W,
+                      int64_t ldw, int64_t N, const float* bias, int relu, void* C,
+                      int64_t ldc, void* ws, size_t ws_bytes, pygb_stream_t s);
 
 /* dW[Kx,Ng] = X[R,Kx]^T . G[R,Ng], fp32 — the weight gradient of `torch.matmul(x,
  * self.weight)` (what `loss.backward()` at examples/gcn.py:39 / ConvexPruning.py:386 computes

@@ -114,6 +114,17 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                        uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32"
@@ -161,8 +172,8 @@ __device__ __forceinline__ uint64_t smem_desc_sw64(uint32_t saddr) {
 struct GemmParams {
   const float* bias;
   int relu;  // max(x, 0) after the bias (NaN stays NaN, like torch.relu)
-  float* C;
-  int64_t ldc;
+  void* C;        // fp32, or bf16 for the bf16 kernel
+  int64_t ldc;    // elements
   int M, N, K;
   int a_kw;       // columns per plane of A (K when A is one row-major matrix)
   int a_3d;       // A is several planes: 3-D tensor map
@@ -186,21 +197,26 @@ struct GemmParams {
 // swizzle atoms): the two 128-row halves share every W tile, so a k-step of 32 moves
 // 2*16 + 2*BN*64*2/1024 KB for 256 rows instead of 16 + 2*BN*128/1024 KB for 128 — 40 % fewer
 // bytes from L2 per flop at BN = 256, where the shared-memory fill rate bounds the main loop.
-template <int PASSES, int MH, int BKT>
+// KIND = 0: fp32 operands, kind::tf32 (1 or 3 passes).  KIND = 1: bf16 operands and bf16
+// output, kind::f16 with fp32 accumulation in TMEM — one pass, no splitter work; BKT counts
+// ELEMENTS per k-step (64 bf16 = one 128-byte swizzle row, 32 bf16 = one 64-byte row).
+template <int PASSES, int MH, int BKT, int KIND = 0>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBh,
                  const __grid_constant__ CUtensorMap mapBl, const GemmParams P) {
   constexpr int kBK = BKT;                        // shadows the namespace constants
+  constexpr int kEsz = KIND == 1 ? 2 : 4;         // operand element size
   constexpr int kTileM = MH * kBM;
-  constexpr int kATileBytes = kTileM * kBK * 4;
-  constexpr bool SW64 = BKT == 16;                // 64-byte rows -> 64-byte swizzle atoms
-  static_assert(BKT == 16 || BKT == 32, "k-step of one 64- or 128-byte swizzle row");
+  constexpr int kATileBytes = kTileM * kBK * kEsz;
+  constexpr bool SW64 = BKT * kEsz == 64;         // 64-byte rows -> 64-byte swizzle atoms
+  static_assert(BKT * kEsz == 64 || BKT * kEsz == 128, "k-step of one 64- or 128-byte swizzle row");
+  static_assert(KIND == 0 || PASSES == 1, "the bf16 kernel is single-pass");
   extern __shared__ __align__(1024) unsigned char gsm[];
   __shared__ __align__(8) uint64_t bars[3 * kMaxStages + 4];
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int BN = P.BN, S = P.stages;
-  const uint32_t b_bytes = (uint32_t)BN * kBK * 4;
+  const uint32_t b_bytes = (uint32_t)BN * kBK * kEsz;
   const uint32_t stage_bytes = (PASSES == 3 ? 2 : 1) * (kATileBytes + b_bytes);
   const uint32_t base = (smem_u32(gsm) + 1023u) & ~1023u;  // swizzle atoms: 1024-byte aligned
   auto a_hi = [&](int s) { return base + (uint32_t)s * stage_bytes; };
@@ -274,7 +290,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
+      // D fp32; A/B format 2 = tf32, 1 = bf16; both K-major
+      constexpr uint32_t kFmt = KIND == 1 ? 1u : 2u;
+      const uint32_t idesc = (1u << 4) | (kFmt << 7) | (kFmt << 10) | ((uint32_t)(BN >> 3) << 17) |
                              ((uint32_t)(kBM >> 4) << 24);
       int it = 0, tl = 0;
       for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++tl) {
@@ -291,14 +309,15 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           const uint64_t dbl = SW64 ? smem_desc_sw64(b_lo(s)) : smem_desc_sw128(b_lo(s));
 #pragma unroll
           for (int h = 0; h < MH; ++h) {       // 128-row halves of the tile share the W stage
-            const uint32_t hoff = (uint32_t)(h * kBM * kBK * 4);
+            const uint32_t hoff = (uint32_t)(h * kBM * kBK * kEsz);
             const uint64_t dah = SW64 ? smem_desc_sw64(a_hi(s) + hoff) : smem_desc_sw128(a_hi(s) + hoff);
             const uint64_t dal = SW64 ? smem_desc_sw64(a_lo(s) + hoff) : smem_desc_sw128(a_lo(s) + hoff);
             const uint32_t dc = dcol + (uint32_t)(h * BN);
 #pragma unroll
-            for (int k = 0; k < kBK / 8; ++k) {  // UMMA_K = 8 tf32 = 32 bytes -> +2 in the address field
+            for (int k = 0; k < kBK * kEsz / 32; ++k) {  // UMMA_K = 8 tf32 / 16 bf16 = 32 bytes -> +2 in the address field
               const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
-              mma_tf32(dc, dah + 2u * k, dbh + 2u * k, idesc, acc);
+              if (KIND == 1) mma_f16(dc, dah + 2u * k, dbh + 2u * k, idesc, acc);
+              else mma_tf32(dc, dah + 2u * k, dbh + 2u * k, idesc, acc);
               if (PASSES == 3) {
                 mma_tf32(dc, dal + 2u * k, dbh + 2u * k, idesc, 1u);
                 mma_tf32(dc, dah + 2u * k, dbl + 2u * k, idesc, 1u);
@@ -352,6 +371,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const uint32_t epi = base + (uint32_t)S * stage_bytes + (uint32_t)(q * kEpiWarpBytes);
     const bool vec_ok = (P.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.C) & 15) == 0);
+    float* const Cf = static_cast<float*>(P.C);
+    __nv_bfloat16* const Cb = static_cast<__nv_bfloat16*>(P.C);
     const int rr = lane >> 3, jj = lane & 7;
     int tl = 0;
     for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++tl) {
@@ -403,14 +424,26 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
             const int row = row0 + rl;
             if (row < P.M && col_ok) {
-              float* dst = P.C + (int64_t)row * P.ldc + col;
-              if (vec_ok && col + 4 <= P.N) {
-                *reinterpret_cast<float4*>(dst) = v;
+              if (KIND == 1) {
+                __nv_bfloat16* dst = Cb + (int64_t)row * P.ldc + col;
+                if (vec_ok && col + 4 <= P.N) {     // 4 bf16 = 8 bytes, 8-byte aligned
+                  *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+                } else {
+                  dst[0] = __float2bfloat16_rn(v.x);
+                  if (col + 1 < P.N) dst[1] = __float2bfloat16_rn(v.y);
+                  if (col + 2 < P.N) dst[2] = __float2bfloat16_rn(v.z);
+                  if (col + 3 < P.N) dst[3] = __float2bfloat16_rn(v.w);
+                }
               } else {
-                dst[0] = v.x;
-                if (col + 1 < P.N) dst[1] = v.y;
-                if (col + 2 < P.N) dst[2] = v.z;
-                if (col + 3 < P.N) dst[3] = v.w;
+                float* dst = Cf + (int64_t)row * P.ldc + col;
+                if (vec_ok && col + 4 <= P.N) {
+                  *reinterpret_cast<float4*>(dst) = v;
+                } else {
+                  dst[0] = v.x;
+                  if (col + 1 < P.N) dst[1] = v.y;
+                  if (col + 2 < P.N) dst[2] = v.z;
+                  if (col + 3 < P.N) dst[3] = v.w;
+                }
               }
             }
           }
@@ -469,6 +502,18 @@ gemm_prep_weight_kernel(const float* __restrict__ W, int64_t ldw, int K, int N, 
   }
 }
 
+// bf16 W [K,N] (row stride ldw) -> Wt [Np][Kp] (K-major, zero padded)
+__global__ void __launch_bounds__(256)
+gemm_prep_weight_bf16_kernel(const __nv_bfloat16* __restrict__ W, int64_t ldw, int K, int N, int Kp,
+                             int Np, __nv_bfloat16* __restrict__ Wt) {
+  const int64_t total = (int64_t)Np * Kp;
+  for (int64_t t = (int64_t)blockIdx.x * 256 + threadIdx.x; t < total;
+       t += (int64_t)gridDim.x * 256) {
+    const int n = (int)(t / Kp), k = (int)(t - (int64_t)n * Kp);
+    Wt[t] = (n < N && k < K) ? W[(int64_t)k * ldw + n] : __float2bfloat16_rn(0.f);
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -489,21 +534,22 @@ EncodeTiledFn encode_fn() {
 }
 
 // 2-D fp32 row-major [rows, cols] with row stride ld (elements); box = [box_rows, 32 cols]
-int make_map(CUtensorMap* map, const float* ptr, int64_t rows, int64_t cols, int64_t ld,
-             int box_rows, int bk, bool atom32 = false) {
+int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t cols, int64_t ld,
+             int box_rows, int bk, bool atom32 = false, int esz = 4) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");
     return PYGB_E_UNSUPPORTED;
   }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
   cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides,
+  CUresult r = fn(map, esz == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                  2, const_cast<void*>(ptr), dims, strides,
                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
-                         : (bk == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B),
+                         : (bk * esz == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B),
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) for [%lld x %lld] ld %lld", (int)r,
@@ -1032,6 +1078,87 @@ int pygb_gemm_xtg(const float* X, int64_t ldx, const float* G, int64_t ldg, int6
   int64_t blocks = ceil_div(Kx * Ng, 256);
   gemm_xtg_reduce_kernel<<<(unsigned)blocks, 256, 0, st>>>(P.part, pl.grid, pl.MH * kBM, pl.BN,
                                                           (int)Kx, (int)Ng, dW, ldw);
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+int pygb_gemm_xw_bf16(const void* A, int64_t lda, int64_t M, int64_t K, const void* W, int64_t ldw,
+                      int64_t N, const float* bias, int relu, void* C, int64_t ldc, void* ws,
+                      size_t ws_bytes, pygb_stream_t s) {
+  PYGB_REQUIRE(M >= 0 && K > 0 && N > 0 && M < (1ll << 31) - 256 && K < (1 << 20) && N < (1 << 20),
+               "pygb_gemm_xw_bf16: bad sizes");
+  PYGB_REQUIRE(lda >= K && ldw >= N && ldc >= N, "pygb_gemm_xw_bf16: bad leading dimensions");
+  if (M == 0) return PYGB_OK;
+  PYGB_REQUIRE(A && W && C && ws, "pygb_gemm_xw_bf16: null pointer");
+  if (!aligned16(A) || (lda % 8) != 0) {
+    set_error("pygb_gemm_xw_bf16: A must be 16-byte aligned with a row stride that is a multiple of 8");
+    return PYGB_E_UNSUPPORTED;
+  }
+  if (ws_bytes < pygb_gemm_weight_workspace(K, N)) {
+    set_error("pygb_gemm_xw_bf16: workspace too small");
+    return PYGB_E_WORKSPACE;
+  }
+  cudaStream_t st = as_stream(s);
+  // k-step: 64 bf16 (128-byte rows) unless 32 wastes less of the last step
+  int bk = 64;
+  if (round_up((int)K, 32) < round_up((int)K, 64) && K > 64) bk = 32;
+  const int Kp = round_up((int)K, 64), Np = round_up((int)N, 16);
+  __nv_bfloat16* Wt = reinterpret_cast<__nv_bfloat16*>(align_up(reinterpret_cast<size_t>(ws), 1024));
+  {
+    int64_t blocks = ceil_div((int64_t)Kp * Np, 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    gemm_prep_weight_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(W), ldw, (int)K, (int)N, Kp, Np, Wt);
+    PYGB_LAUNCH_CHECK();
+  }
+  GemmParams P;
+  P.bias = bias;
+  P.relu = relu != 0;
+  P.c_tab = nullptr;
+  P.c_fc = 1;
+  P.c_dup = 0;
+  P.c_row0 = 0;
+  P.c_ldd = 0;
+  P.C = C;
+  P.ldc = ldc;
+  P.M = (int)M;
+  P.N = (int)N;
+  P.K = (int)K;
+  P.a_kw = (int)K;
+  P.a_3d = 0;
+  P.BN = Np < 256 ? Np : 256;
+  P.n_tiles = (int)ceil_div(Np, P.BN);
+  int sms = 148, dev = 0;
+  PYGB_CUDA(cudaGetDevice(&dev));
+  PYGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  P.acc_bufs = 2 * P.BN <= 512 ? 2 : 1;
+  int tc = 32;
+  while (tc < P.acc_bufs * P.BN) tc <<= 1;
+  P.tmem_cols = tc;
+  P.m_tiles = (int)ceil_div(M, kBM);
+  const size_t stage_bytes = (size_t)(kBM + P.BN) * bk * 2;
+  int stages = (int)((226 * 1024 - 1024 - kEpiBytes) / stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  const int nk = (int)ceil_div(K, bk);
+  if (stages > nk) stages = nk < 2 ? 2 : nk;
+  P.stages = stages;
+  const size_t smem = stages * stage_bytes + kEpiBytes + 1024;
+  CUtensorMap mapA, mapB;
+  int rc = make_map(&mapA, A, M, K, lda, kBM, bk, false, 2);
+  if (rc) return rc;
+  rc = make_map(&mapB, Wt, Np, Kp, Kp, P.BN, bk, false, 2);
+  if (rc) return rc;
+  const int64_t tiles = (int64_t)P.m_tiles * P.n_tiles;
+  dim3 grid((unsigned)(tiles < sms ? tiles : sms));
+  if (bk == 64) {
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<1, 1, 64, 1>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(226 * 1024)));
+    gemm_tf32_kernel<1, 1, 64, 1><<<grid, kGemmThreads, smem, st>>>(mapA, mapB, mapB, P);
+  } else {
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<1, 1, 32, 1>,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(226 * 1024)));
+    gemm_tf32_kernel<1, 1, 32, 1><<<grid, kGemmThreads, smem, st>>>(mapA, mapB, mapB, P);
+  }
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }

@@ -144,6 +144,29 @@ __global__ void __launch_bounds__(kThreads) count_loops_kernel(const int64_t* __
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, (unsigned long long)c);
 }
 
+// out[0] += edges with row == col, out[1] += edges with an id outside [0, N)
+__global__ void __launch_bounds__(kThreads) scan_edges_kernel(const int64_t* __restrict__ row,
+                                                              const int64_t* __restrict__ col,
+                                                              int64_t E, int64_t N,
+                                                              unsigned long long* __restrict__ out) {
+  int c = 0, bad = 0;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < E;
+       i += (int64_t)gridDim.x * kThreads) {
+    const int64_t r = row[i], q = col[i];
+    c += (r == q);
+    bad += (r < 0 || r >= N || q < 0 || q >= N);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    c += __shfl_xor_sync(kFull, c, o);
+    bad += __shfl_xor_sync(kFull, bad, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (c) atomicAdd(out, (unsigned long long)c);
+    if (bad) atomicAdd(out + 1, (unsigned long long)bad);
+  }
+}
+
 // per tile: number of kept (row != col) edges
 __global__ void __launch_bounds__(kThreads) keep_count_kernel(const int64_t* __restrict__ row,
                                                               const int64_t* __restrict__ col,
@@ -496,6 +519,18 @@ int pygb_count_self_loops(const int64_t* edge_index, int64_t E, int64_t* d_count
   if (E == 0) return PYGB_OK;
   count_loops_kernel<<<grid_for(E), kThreads, 0, st>>>(
       edge_index, edge_index + E, E, reinterpret_cast<unsigned long long*>(d_count));
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
+}
+
+int pygb_scan_edge_index(const int64_t* edge_index, int64_t E, int64_t N, int64_t* d_out,
+                         pygb_stream_t s) {
+  PYGB_REQUIRE(E >= 0 && N >= 0 && d_out, "pygb_scan_edge_index: bad arguments");
+  cudaStream_t st = as_stream(s);
+  PYGB_CUDA(cudaMemsetAsync(d_out, 0, 2 * sizeof(int64_t), st));
+  if (E == 0) return PYGB_OK;
+  scan_edges_kernel<<<grid_for(E), kThreads, 0, st>>>(
+      edge_index, edge_index + E, E, N, reinterpret_cast<unsigned long long*>(d_out));
   PYGB_LAUNCH_CHECK();
   return PYGB_OK;
 }

@@ -26,6 +26,7 @@ SIGNATURES = {
     'pygb_last_error': (_c.c_char_p, []),
     'pygb_check_device': (_I, [_P, _P, _P]),
     'pygb_count_self_loops': (_I, [_P, _L, _P, _P]),
+    'pygb_scan_edge_index': (_I, [_P, _L, _L, _P, _P]),
     'pygb_apply_loops_workspace': (_Z, [_L, _L]),
     'pygb_apply_loops': (_I, [_P, _L, _L, _I, _L, _P, _F, _P, _P, _P, _Z, _P]),
     'pygb_csr_build_workspace': (_Z, [_L, _L]),
@@ -56,6 +57,7 @@ SIGNATURES = {
                                  _P, _Z, _P]),
     'pygb_seg_gather_reduce_heads': (_I, [_I, _P, _L, _I, _I, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
     'pygb_gather_rows': (_I, [_I, _P, _L, _L, _P, _L, _P, _L, _P]),
+    'pygb_edge_dot': (_I, [_I, _P, _L, _P, _L, _L, _P, _P, _P, _L, _L, _P, _P]),
     'pygb_seg_max': (_I, [_I, _P, _L, _L, _P, _P, _P, _L, _L, _F, _I, _P, _L, _P, _P]),
     'pygb_seg_max_backward': (_I, [_P, _L, _P, _L, _L, _L, _P, _L, _P]),
     'pygb_edge_softmax': (_I, [_P, _L, _P, _P, _L, _P, _P]),
@@ -72,6 +74,7 @@ SIGNATURES = {
     'pygb_gat_alpha': (_I, [_P, _P, _I, _F, _P, _P, _P, _L, _P, _P, _P, _P]),
     'pygb_gemm_weight_workspace': (_Z, [_L, _L]),
     'pygb_gemm_xw': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _P, _Z, _P]),
+    'pygb_gemm_xw_bf16': (_I, [_P, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _P, _Z, _P]),
     'pygb_knn_graph': (_I, [_P, _L, _L, _I, _P, _P, _I, _I, _P, _P]),
     'pygb_gemm_xtg_workspace': (_Z, [_L, _L, _L]),
     'pygb_gemm_xtg': (_I, [_P, _L, _P, _L, _L, _L, _L, _P, _L, _I, _P, _Z, _P]),
@@ -118,7 +121,7 @@ def load():
             fn = getattr(lib, name)
             fn.restype = res
             fn.argtypes = args
-        if lib.pygb_abi_version() != 3:
+        if lib.pygb_abi_version() != 4:
             raise NativeError('libpygb.so ABI version mismatch')
         _lib = lib
     return _lib

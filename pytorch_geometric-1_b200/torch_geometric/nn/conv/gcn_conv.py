@@ -54,6 +54,18 @@ class GCNConv(MessagePassing):
         the reference; weighted degrees are summed in ascending edge order."""
         dev = nat.require_cuda(edge_index, edge_weight)
         fill_value = 1 if not improved else 2
+        if edge_weight is not None and edge_weight.requires_grad and torch.is_grad_enabled():
+            # learnable edge weights: the same formula from differentiable pieces — the native
+            # scatter_add (deterministic, gather backward) and the native row gather
+            # (atomic-free backward); values match the fused kernels up to fp32 rounding
+            edge_index, w = add_remaining_self_loops(edge_index, edge_weight.float(), fill_value,
+                                                     num_nodes)
+            row, col = edge_index[0], edge_index[1]
+            deg = ops.segment_reduce(w, row, int(num_nodes), 'add')
+            dis = deg.pow(-0.5)
+            dis = dis.masked_fill(dis == float('inf'), 0)
+            norm = ops.index_select0(dis, row) * w * ops.index_select0(dis, col)
+            return edge_index, norm if dtype in (None, torch.float32) else norm.to(dtype)
         unit = edge_weight is None and not improved
         if edge_weight is None and not unit:
             edge_weight = torch.ones((edge_index.size(1),), dtype=torch.float32, device=dev)

@@ -66,13 +66,13 @@ class ChebConv(_WeightedSum):
     def forward(self, x, edge_index, edge_weight=None):
         edge_index, norm = self.norm(edge_index, x.size(self.node_dim), edge_weight, x.dtype)
         Tx_0 = x
-        out = torch.matmul(Tx_0, self.weight[0])
+        out = ops.linear(Tx_0, self.weight[0])
         if self.weight.size(0) > 1:
             Tx_1 = self.propagate(edge_index, x=x, norm=norm)
-            out = out + torch.matmul(Tx_1, self.weight[1])
+            out = out + ops.linear(Tx_1, self.weight[1])
         for k in range(2, self.weight.size(0)):
             Tx_2 = 2 * self.propagate(edge_index, x=Tx_1, norm=norm) - Tx_0
-            out = out + torch.matmul(Tx_2, self.weight[k])
+            out = out + ops.linear(Tx_2, self.weight[k])
             Tx_0, Tx_1 = Tx_1, Tx_2
         if self.bias is not None:
             out = out + self.bias
@@ -96,7 +96,7 @@ class GraphConv(_WeightedSum):
         self.lin.reset_parameters()
 
     def forward(self, x, edge_index, edge_weight=None, size=None):
-        h = torch.matmul(x, self.weight)
+        h = ops.linear(x, self.weight)
         return self.propagate(edge_index, size=size, x=x, h=h, norm=edge_weight)
 
     def _fused_propagate(self, edge_index, size, i, kwargs):
@@ -197,7 +197,7 @@ class SAGEConv(MessagePassing):
         elif self.concat and isinstance(x, (tuple, list)):
             assert x[1] is not None
             aggr_out = torch.cat([x[1], aggr_out], dim=-1)
-        aggr_out = torch.matmul(aggr_out, self.weight)
+        aggr_out = ops.linear(aggr_out, self.weight)
         if self.bias is not None:
             aggr_out = aggr_out + self.bias
         if self.normalize:

@@ -4,6 +4,7 @@ These are the pieces ``MessagePassing.propagate``, ``utils.scatter_`` and
 ``utils.softmax`` are assembled from.  Everything here launches kernels of
 ``libpygb.so`` on the tensor's current CUDA stream; there is no CPU path.
 """
+import collections
 import os
 
 import torch
@@ -209,6 +210,22 @@ def gather_rows_raw(x, index):
     return out
 
 
+def edge_dot_raw(g, x, csr):
+    """``out[e] = <g[dst_e], x[src_e]>`` (fp32 ``[E]``, original edge order) over the
+    destination-sorted ``csr`` (pygb_edge_dot)."""
+    dev = nat.require_cuda(g, x)
+    g2, x2 = _rows2d(g), _rows2d(x)
+    if g2.dtype != x2.dtype:
+        g2, x2 = g2.float(), x2.float()
+    assert g2.size(1) == x2.size(1) and g2.size(0) == csr.n_rows
+    out = torch.empty((csr.E,), dtype=torch.float32, device=dev)
+    if csr.E > 0:
+        nat.call('pygb_edge_dot', dev, nat.dtype_code(g2), nat.ptr(g2), _ld(g2), nat.ptr(x2),
+                 _ld(x2), g2.size(1), nat.ptr(csr.rowptr), nat.ptr(csr.col), nat.ptr(csr.perm),
+                 csr.n_rows, csr.E, nat.ptr(out))
+    return out
+
+
 def seg_max_raw(src, csr, idx, eid, e_fill, zero_below=NEG_INF, mask_arg=False, want_arg=True):
     dev = nat.require_cuda(src, idx, eid)
     s2 = _rows2d(src)
@@ -256,10 +273,8 @@ class _GatherReduce(torch.autograd.Function):
             gx = seg_gather_reduce_raw(gs, adj.src, adj.src.col, 'sum', w_t, None, None)
             gx = _unflat(gx, adj.n_src, ctx.xshape[1:])
         if w is not None and ctx.needs_input_grad[1]:
-            ei = adj.edge_index
-            gi = gather_rows_raw(gs, ei[adj.i])
-            xj = gather_rows_raw(x, ei[adj.j])
-            gw = (gi.float() * xj.float()).sum(1).to(w.dtype)
+            # d/dw_e = <g[dst_e], x[src_e]>: one walk over the sorted graph, no [E, F] tensor
+            gw = edge_dot_raw(gs, x, adj.dst).to(w.dtype)
         return gx, gw, gb, None, None
 
 
@@ -560,6 +575,9 @@ def gat_propagate(x_src, x_dst, att, bias, adj, H, C, slope):
 # --------------------------------------------------------------------------
 # '3' = 3xTF32 split (fp32-faithful, default), '1' = plain TF32, '0' = library GEMM.
 GEMM_PASSES = int(os.environ.get('PYGB_GEMM', '3'))
+# PYGB_STRICT_GEMM=1: `linear` raises instead of handing anything to the library GEMM
+# (tests use it to prove that a configuration runs on the tcgen05 kernels).
+STRICT_GEMM = os.environ.get('PYGB_STRICT_GEMM', '0') not in ('', '0')
 
 
 def _pad4(n, itemsize):
@@ -568,16 +586,51 @@ def _pad4(n, itemsize):
 
 
 def _gemm_eligible(x, w):
-    """2-D fp32 CUDA operands with 16-byte aligned rows; ``x`` may also be slice-major:
-    ``[S, M, Kc]`` planes of ``Kc`` (multiple of 32) columns, standing for ``[M, S*Kc]``."""
-    ok = (GEMM_PASSES in (1, 3) and x.is_cuda and w.dim() == 2
-          and x.dtype == torch.float32 and w.dtype == torch.float32 and x.size(-2) > 0
-          and x.size(-1) > 0 and w.size(1) > 0 and x.stride(-1) == 1 and x.stride(-2) % 4 == 0
+    """fp32 (tf32 kernel) or bf16 (f16-kind kernel) CUDA operands of one dtype with 16-byte
+    aligned rows; an fp32 ``x`` may also be slice-major: ``[S, M, Kc]`` planes of ``Kc``
+    (multiple of 32) columns, standing for ``[M, S*Kc]`` (internal callers only)."""
+    vec = 16 // x.element_size()
+    ok = (GEMM_PASSES in (1, 3) and x.is_cuda and w.dim() == 2 and x.dtype == w.dtype
+          and x.dtype in (torch.float32, torch.bfloat16) and x.size(-2) > 0
+          and x.size(-1) > 0 and w.size(1) > 0 and x.stride(-1) == 1 and x.stride(-2) % vec == 0
           and x.stride(-2) >= x.size(-1) and x.data_ptr() % 16 == 0 and w.stride(1) == 1)
     if x.dim() == 3:
-        return (ok and x.size(2) % 32 == 0 and x.stride(0) % 4 == 0
+        return (ok and x.dtype == torch.float32 and x.size(2) % 32 == 0 and x.stride(0) % 4 == 0
                 and x.stride(0) >= x.stride(1) * x.size(1))
     return ok and x.dim() == 2
+
+
+_pad_cache = collections.OrderedDict()      # identity of a constant input -> its padded copy
+
+
+def _aligned_rows(x, cache=True):
+    """``x`` [M, K] as a tensor whose rows start on 16-byte boundaries (what TMA needs):
+    ``x`` itself, or the ``[:, :K]`` view of a zero-padded copy ``[M, Kp]``.  K = 602 or 1433
+    fp32 rows (BASELINE cfg3 / cfg1) are not 16-byte multiples.  For an input that does not
+    require grad (dataset features) the copy is made once and memoised on the tensor's
+    identity, like the sorted graph; otherwise it is a differentiable ``F.pad``."""
+    vec = 16 // x.element_size()
+    if x.stride(1) == 1 and x.stride(0) % vec == 0 and x.stride(0) >= x.size(1) \
+            and x.data_ptr() % 16 == 0:
+        return x
+    K = x.size(1)
+    Kp = (K + vec - 1) // vec * vec
+    if x.requires_grad and torch.is_grad_enabled():
+        return torch.nn.functional.pad(x, (0, Kp - K))[:, :K]
+    key = (x.data_ptr(), tuple(x.shape), tuple(x.stride()), x._version, x.device.index, x.dtype)
+    if cache:
+        hit = _pad_cache.get(key)
+        if hit is not None:
+            _pad_cache.move_to_end(key)
+            return hit[0]
+    xp = x.new_zeros((x.size(0), Kp))
+    xp[:, :K].copy_(x)
+    out = xp[:, :K]
+    if cache:
+        _pad_cache[key] = (out, x)           # keeps x alive: the pointer cannot be recycled
+        while len(_pad_cache) > 4:
+            _pad_cache.popitem(last=False)
+    return out
 
 
 def _gemm_a_args(x, rows=None):
@@ -592,25 +645,31 @@ def _gemm_a_args(x, rows=None):
 def gemm_xw_raw(x, w, bias=None, passes=None, out=None, relu=False, rows=None):
     """``x @ w (+ bias)`` by the tcgen05 kernel; the result's rows are padded to 16 bytes
     (a view ``[:, :N]`` is returned) so that a following aggregation stays vectorised.
-    ``out``: optional ``[M, >=N]`` fp32 destination with unit inner stride (written in place).
-    ``x``: ``[M, K]`` or slice-major ``[S, >=M, K/S]`` (``rows`` = M)."""
+    ``out``: optional ``[M, >=N]`` destination of x's dtype with unit inner stride.
+    ``x``: ``[M, K]`` fp32 / bf16, or fp32 slice-major ``[S, >=M, K/S]`` (``rows`` = M)."""
     dev = nat.require_cuda(x, w, bias)
     a_ptr, lda, a_slices, a_plane, M, K = _gemm_a_args(x, rows)
     N = w.size(1)
-    assert w.size(0) == K
+    assert w.size(0) == K and w.dtype == x.dtype
+    esz = x.element_size()
     if out is None:
-        ldc = _pad4(N, 4)
-        out_full = torch.empty((M, ldc), dtype=torch.float32, device=dev)
+        ldc = _pad4(N, esz)
+        out_full = torch.empty((M, ldc), dtype=x.dtype, device=dev)
     else:
-        assert out.dtype == torch.float32 and out.size(0) == M and out.size(1) >= N
+        assert out.dtype == x.dtype and out.size(0) == M and out.size(1) >= N
         assert out.stride(1) == 1
         out_full, ldc = out, (out.stride(0) if M > 1 else max(out.size(1), 1))
     ws_bytes = nat.workspace('pygb_gemm_weight_workspace', K, N)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     b = _f32(bias)
-    nat.call('pygb_gemm_xw', dev, a_ptr, lda, a_slices, a_plane, M, K, nat.ptr(w), w.stride(0), N,
-             nat.ptr(b), int(bool(relu)), nat.ptr(out_full), ldc, int(passes or GEMM_PASSES),
-             nat.ptr(ws), ws_bytes)
+    if x.dtype == torch.bfloat16:
+        assert x.dim() == 2
+        nat.call('pygb_gemm_xw_bf16', dev, a_ptr, lda, M, K, nat.ptr(w), w.stride(0), N,
+                 nat.ptr(b), int(bool(relu)), nat.ptr(out_full), ldc, nat.ptr(ws), ws_bytes)
+    else:
+        nat.call('pygb_gemm_xw', dev, a_ptr, lda, a_slices, a_plane, M, K, nat.ptr(w),
+                 w.stride(0), N, nat.ptr(b), int(bool(relu)), nat.ptr(out_full), ldc,
+                 int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
     return out_full[:, :N] if out_full.size(1) != N else out_full
 
 
@@ -618,7 +677,7 @@ def _xtg_eligible(x, g):
     return (GEMM_PASSES in (1, 3) and x.is_cuda and x.dim() == 2 and g.dim() == 2
             and x.dtype == torch.float32 and g.dtype == torch.float32
             and x.size(0) == g.size(0) and x.size(0) >= 1024
-            and 0 < x.size(1) <= 256 and 0 < g.size(1) <= 256
+            and 0 < x.size(1) and 0 < g.size(1)
             and x.stride(1) == 1 and g.stride(1) == 1 and x.stride(0) % 4 == 0
             and g.stride(0) % 4 == 0 and x.stride(0) >= x.size(1) and g.stride(0) >= g.size(1)
             and x.data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0)
@@ -626,14 +685,22 @@ def _xtg_eligible(x, g):
 
 def gemm_xtg_raw(x, g, passes=None):
     """``x.t() @ g`` (the weight gradient) by the split-K tcgen05 kernel: both operands are
-    read once, row-major as they are (MN-major tensor-core operands)."""
+    read row-major as they are (MN-major tensor-core operands).  The kernel keeps a
+    ``[<=256, <=256]`` partial in TMEM; wider outputs are tiled over column blocks of x / g
+    (views with the same row stride — nothing is copied)."""
     dev = nat.require_cuda(x, g)
     R, Kx, Ng = x.size(0), x.size(1), g.size(1)
     out = torch.empty((Kx, Ng), dtype=torch.float32, device=dev)
-    ws_bytes = nat.workspace('pygb_gemm_xtg_workspace', R, Kx, Ng)
-    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    nat.call('pygb_gemm_xtg', dev, nat.ptr(x), x.stride(0), nat.ptr(g), g.stride(0), R, Kx, Ng,
-             nat.ptr(out), Ng, int(passes or GEMM_PASSES), nat.ptr(ws), ws_bytes)
+    for k0 in range(0, Kx, 256):
+        k1 = min(k0 + 256, Kx)
+        for n0 in range(0, Ng, 256):
+            n1 = min(n0 + 256, Ng)
+            xs, gs, o = x[:, k0:k1], g[:, n0:n1], out[k0:k1, n0:n1]
+            ws_bytes = nat.workspace('pygb_gemm_xtg_workspace', R, k1 - k0, n1 - n0)
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            nat.call('pygb_gemm_xtg', dev, nat.ptr(xs), x.stride(0), nat.ptr(gs), g.stride(0), R,
+                     k1 - k0, n1 - n0, nat.ptr(o), Ng, int(passes or GEMM_PASSES), nat.ptr(ws),
+                     ws_bytes)
     return out
 
 
@@ -648,17 +715,19 @@ class _Linear(torch.autograd.Function):
     def backward(ctx, g):
         x, w = ctx.saved_tensors
         gx = gw = gb = None
+        ga = None
+        if g.dim() == 2 and g.dtype == x.dtype:
+            ga = _aligned_rows(g if g.stride(-1) == 1 else g.contiguous(), cache=False)
         if ctx.needs_input_grad[0]:
             wt = w.t().contiguous()
-            g2 = g if g.stride(-1) == 1 else g.contiguous()
-            if _gemm_eligible(g2, wt):              # dX = g W^T on the same tcgen05 kernel
-                gx = gemm_xw_raw(g2, wt)
+            if ga is not None and _gemm_eligible(ga, wt):    # dX = g W^T on the same kernel
+                gx = gemm_xw_raw(ga, wt)
                 gx = gx if gx.is_contiguous() else gx.contiguous()
             else:
                 gx = torch.matmul(g, w.t())
         if ctx.needs_input_grad[1]:
-            if _xtg_eligible(x, g):                 # dW = x^T g: split-K over the rows on tcgen05
-                gw = gemm_xtg_raw(x, g)
+            if ga is not None and _xtg_eligible(x, ga):      # dW = x^T g: split-K on tcgen05
+                gw = gemm_xtg_raw(x, ga)
             else:
                 gw = torch.matmul(x.t(), g)
         if ctx.has_bias and ctx.needs_input_grad[2]:
@@ -667,11 +736,20 @@ class _Linear(torch.autograd.Function):
 
 
 def linear(x, w, bias=None):
-    """``x @ w (+ bias)`` (the X·W of GCNConv / GATConv).  fp32 2-D CUDA inputs with
-    16-byte aligned rows go to the tcgen05 kernel; anything else to the library GEMM,
-    with the output row padded the same way."""
-    if _gemm_eligible(x, w):
-        return _Linear.apply(x, w, bias)
+    """``x @ w (+ bias)`` (the X·W of GCNConv / GATConv).  2-D fp32 / bf16 CUDA inputs run on
+    the tcgen05 kernels (rows that are not 16-byte multiples through one padded copy, see
+    ``_aligned_rows``); the output row is padded to 16 bytes.  Anything else (other dtypes,
+    ``[N, T, F]`` inputs) is ``torch.matmul`` — or an error under ``PYGB_STRICT_GEMM=1``."""
+    if (x.dim() == 2 and w.dim() == 2 and x.is_cuda and x.dtype == w.dtype
+            and x.dtype in (torch.float32, torch.bfloat16) and x.numel() > 0 and w.numel() > 0
+            and GEMM_PASSES in (1, 3)):
+        xa = _aligned_rows(x)
+        wa = w if w.stride(1) == 1 else w.contiguous()
+        if _gemm_eligible(xa, wa):
+            return _Linear.apply(xa, wa, bias)
+    if STRICT_GEMM:
+        raise RuntimeError('ops.linear: {} x {} ({}, {}) would fall back to the library GEMM'.format(
+            tuple(x.shape), tuple(w.shape), x.dtype, x.device))
     pad = 0
     if x.dim() == 2 and x.is_floating_point():
         pad = _pad4(w.size(1), x.element_size()) - w.size(1)

@@ -9,11 +9,23 @@ from .. import _native as nat
 from .num_nodes import maybe_num_nodes
 
 
-def _count_loops(edge_index):
+def _count_loops(edge_index, num_nodes=None):
+    """Number of self-loops; with ``num_nodes`` the same pass also range-checks every id
+    (IndexError) — one device->host read for both."""
     dev = edge_index.device
-    cnt = torch.empty(1, dtype=torch.long, device=dev)
-    nat.call('pygb_count_self_loops', dev, nat.ptr(edge_index), edge_index.size(1), nat.ptr(cnt))
-    return int(cnt.item())
+    if num_nodes is None:
+        cnt = torch.empty(1, dtype=torch.long, device=dev)
+        nat.call('pygb_count_self_loops', dev, nat.ptr(edge_index), edge_index.size(1),
+                 nat.ptr(cnt))
+        return int(cnt.item())
+    cnt = torch.empty(2, dtype=torch.long, device=dev)
+    nat.call('pygb_scan_edge_index', dev, nat.ptr(edge_index), edge_index.size(1),
+             int(num_nodes), nat.ptr(cnt))
+    loops, bad = cnt.tolist()
+    if bad:
+        raise IndexError('edge_index holds {} edge(s) with a node id outside [0, {})'.format(
+            bad, int(num_nodes)))
+    return int(loops)
 
 
 def _apply(edge_index, N, mode, edge_weight, fill_value):
@@ -22,7 +34,9 @@ def _apply(edge_index, N, mode, edge_weight, fill_value):
         raise ValueError('edge_index must be an int64 tensor of shape [2, E]')
     edge_index = edge_index if edge_index.is_contiguous() else edge_index.contiguous()
     E = edge_index.size(1)
-    n_loops = _count_loops(edge_index) if (mode != nat.LOOPS_ADD and E > 0) else 0
+    n_loops = 0
+    if mode != nat.LOOPS_ADD and E > 0:
+        n_loops = _count_loops(edge_index, N if mode != nat.LOOPS_REMOVE else None)
     keep = E - n_loops if mode != nat.LOOPS_ADD else E
     e_out = keep + (N if mode != nat.LOOPS_REMOVE else 0)
     out = torch.empty((2, e_out), dtype=torch.long, device=dev)
@@ -39,6 +53,34 @@ def _apply(edge_index, N, mode, edge_weight, fill_value):
     return out, w_out, n_loops
 
 
+def _needs_grad(w):
+    return w is not None and w.requires_grad and torch.is_grad_enabled()
+
+
+def _weights_with_grad(edge_index, w, mode, fill_value, N):
+    """The float side of ``_apply`` as differentiable indexing of ``w`` (pure copies, so the
+    values equal the native kernel's): used only when ``w.requires_grad`` — the native call
+    still produces the integer ``edge_index'``.  Every source element is read at most once,
+    so the backward (index_put with unique indices) is deterministic."""
+    row, col = edge_index[0], edge_index[1]
+    if mode == nat.LOOPS_ADD:
+        return torch.cat([w, w.new_full((N,), fill_value)])
+    mask = row != col
+    kept = w[mask]
+    if mode == nat.LOOPS_REMOVE:
+        return kept
+    loop_w = w.new_full((N,), fill_value)
+    if mode == nat.LOOPS_ADD_REMAINING:
+        inv = ~mask
+        pos = torch.arange(row.numel(), device=row.device)[inv]
+        # several existing loops on one node: the highest edge id wins (Q1, last write)
+        last = torch.full((N,), -1, dtype=torch.long, device=row.device)
+        last.scatter_reduce_(0, row[inv], pos, 'amax', include_self=True)
+        has = last >= 0
+        loop_w = torch.where(has, w[last.clamp(min=0)], loop_w)
+    return torch.cat([kept, loop_w])
+
+
 def contains_self_loops(edge_index):
     nat.require_cuda(edge_index)
     ei = edge_index if edge_index.is_contiguous() else edge_index.contiguous()
@@ -53,6 +95,9 @@ def remove_self_loops(edge_index, edge_attr=None):
             raise ValueError('remove_self_loops: edge_attr of this shape needs E < 2^24')
         out, kept, _ = _apply(edge_index, 0, nat.LOOPS_REMOVE, ids, 0.0)
         return out, edge_attr[kept.long()]
+    if _needs_grad(edge_attr):
+        out, _, _ = _apply(edge_index, 0, nat.LOOPS_REMOVE, None, 0.0)
+        return out, _weights_with_grad(edge_index, edge_attr, nat.LOOPS_REMOVE, 0.0, 0)
     out, w, _ = _apply(edge_index, 0, nat.LOOPS_REMOVE, edge_attr, 0.0)
     return out, w
 
@@ -61,6 +106,9 @@ def add_self_loops(edge_index, edge_weight=None, fill_value=1, num_nodes=None):
     n = maybe_num_nodes(edge_index, num_nodes)
     if edge_weight is not None:
         assert edge_weight.numel() == edge_index.size(1)
+    if _needs_grad(edge_weight):
+        out, _, _ = _apply(edge_index, n, nat.LOOPS_ADD, None, fill_value)
+        return out, _weights_with_grad(edge_index, edge_weight, nat.LOOPS_ADD, fill_value, n)
     out, w, _ = _apply(edge_index, n, nat.LOOPS_ADD, edge_weight, fill_value)
     return out, w
 
@@ -69,5 +117,9 @@ def add_remaining_self_loops(edge_index, edge_weight=None, fill_value=1, num_nod
     n = maybe_num_nodes(edge_index, num_nodes)
     if edge_weight is not None:
         assert edge_weight.numel() == edge_index.size(1)
+    if _needs_grad(edge_weight):
+        out, _, _ = _apply(edge_index, n, nat.LOOPS_ADD_REMAINING, None, fill_value)
+        return out, _weights_with_grad(edge_index, edge_weight, nat.LOOPS_ADD_REMAINING,
+                                       fill_value, n)
     out, w, _ = _apply(edge_index, n, nat.LOOPS_ADD_REMAINING, edge_weight, fill_value)
     return out, w

@@ -26,7 +26,7 @@ def test_header_symbols_exported():
         assert hasattr(lib, n), 'missing export {}'.format(n)
     # and the ctypes table covers the header one to one
     assert sorted(_native.SIGNATURES) == names
-    assert lib.pygb_abi_version() == 3
+    assert lib.pygb_abi_version() == 4
 
 
 def test_no_cpu_fallback():

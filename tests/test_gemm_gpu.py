@@ -205,3 +205,105 @@ def test_gemm_xtg_full_size_accuracy(dev):
     lib = torch.matmul(x.t(), g)
     err_lib = (lib.double() - ref).abs().max().item() / ref.abs().max().item()
     print('xtg rel err %.2e, library fp32 GEMM %.2e' % (err, err_lib))
+
+
+BF16_SHAPES = [(1000, 100, 256), (777, 256, 256), (300, 256, 47), (5000, 602, 64), (129, 32, 16),
+               (1, 8, 3), (4097, 64, 8), (256, 1433, 7), (2000, 96, 300), (333, 72, 40)]
+
+
+@pytest.mark.parametrize('M,K,N', BF16_SHAPES)
+def test_gemm_bf16_matches_fp64_of_the_bf16_inputs(dev, M, K, N):
+    """kind::f16 kernel (VERDICT r01 #1: bf16 had no tensor-core transform).  Reference: fp64
+    product of the SAME bf16-rounded operands — what is left is fp32 accumulation order and
+    the bf16 rounding of the result (2^-9 relative), far inside north_star's 1e-2 bf16 bar."""
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(M + K + N)
+    x = torch.randn(M, K, generator=g).bfloat16()
+    w = (torch.randn(K, N, generator=g) / K ** 0.5).bfloat16()
+    b = torch.randn(N, generator=g)
+    xd = ops._aligned_rows(x.to(dev))
+    assert ops._gemm_eligible(xd, w.to(dev))
+    got = ops.gemm_xw_raw(xd, w.to(dev), b.to(dev))
+    assert got.dtype == torch.bfloat16 and got.shape == (M, N)
+    ref = x.double() @ w.double() + b.double()
+    err = (got.double().cpu() - ref).abs()
+    bound = 2.0 ** -8 * ref.abs() + 1e-3 * ref.abs().max()
+    assert bool((err <= bound).all()), float((err / bound).max())
+    fused = ops.gemm_xw_raw(xd, w.to(dev), b.to(dev), relu=True)
+    assert torch.equal(fused, torch.relu(got))
+
+
+@pytest.mark.parametrize('K', [602, 1433, 7, 33, 101])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_linear_unaligned_k_runs_on_tcgen05(dev, K, dtype):
+    """BASELINE cfg3 (K = 602) and cfg1 (K = 1433): rows that are not 16-byte multiples reach
+    the tensor-core kernel through one memoised padded copy — asserted on the native event
+    log, under PYGB_STRICT_GEMM semantics (no library GEMM), forward and backward."""
+    from torch_geometric import _native as nat
+    from torch_geometric import ops
+    M, N = 1500, 64
+    g = torch.Generator().manual_seed(K)
+    x = torch.randn(M, K, generator=g).to(dtype)
+    w = (torch.randn(K, N, generator=g) / K ** 0.5).to(dtype)
+    b = torch.randn(N, generator=g).to(dtype)
+    xd = x.to(dev)
+    wd = w.to(dev).requires_grad_(True)
+    bd = b.to(dev).requires_grad_(True)
+    old, ops.STRICT_GEMM = ops.STRICT_GEMM, True
+    nat.event_log = []
+    try:
+        out = ops.linear(xd, wd, bd)
+        names = [e[0] for e in nat.event_log]
+        again = ops.linear(xd, wd, bd)
+    finally:
+        ops.STRICT_GEMM = old
+        log, nat.event_log = nat.event_log, None
+    want = 'pygb_gemm_xw_bf16' if dtype == torch.bfloat16 else 'pygb_gemm_xw'
+    assert names == [want], names
+    assert torch.equal(out, again)
+    assert out.shape == (M, N)
+    ref = x.double() @ w.double() + b.double()
+    tol = 1e-5 if dtype == torch.float32 else 2.0 ** -7
+    err = (out.double().cpu() - ref).abs()
+    assert bool((err <= tol * ref.abs() + tol * ref.abs().max()).all())
+    # the padded copy of a constant input is made once
+    if K % (16 // x.element_size()):
+        assert ops._aligned_rows(xd).data_ptr() == ops._aligned_rows(xd).data_ptr()
+    gout = torch.randn(M, N, generator=g).to(dtype)
+    out.backward(gout.to(dev))
+    ref_gw = x.double().t() @ gout.double()
+    err = (wd.grad.double().cpu() - ref_gw).abs()
+    gtol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert bool((err <= gtol * ref_gw.abs() + gtol * ref_gw.abs().max()).all())
+    assert wd.grad.shape == (K, N) and bd.grad.shape == (N,)
+
+
+def test_linear_unaligned_input_that_requires_grad(dev):
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(900, 602, generator=g)
+    w = torch.randn(602, 40, generator=g) / 25
+    xd = x.to(dev).requires_grad_(True)
+    wd = w.to(dev).requires_grad_(True)
+    out = ops.linear(xd, wd)
+    gout = torch.randn(900, 40, generator=g)
+    out.backward(gout.to(dev))
+    xr, wr = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    (xr @ wr).backward(gout.double())
+    for got, ref, what in ((xd.grad, xr.grad, 'dx'), (wd.grad, wr.grad, 'dw')):
+        assert got.shape == ref.shape
+        err = (got.double().cpu() - ref).abs()
+        assert bool((err <= 1e-5 * ref.abs() + 1e-5 * ref.abs().max()).all()), what
+
+
+def test_gemm_xtg_tiles_wide_outputs(dev):
+    """dW for K > 256 (cfg3: 602 x 64) stays on the split-K tcgen05 kernel, tiled over column
+    blocks of x (views, nothing copied)."""
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(3000, 604, generator=g)
+    gr = torch.randn(3000, 300, generator=g)
+    got = ops.gemm_xtg_raw(x.to(dev), gr.to(dev))
+    ref = x.double().t() @ gr.double()
+    assert got.shape == (604, 300)
+    assert (got.double().cpu() - ref).abs().max().item() / ref.abs().max().item() <= 1e-5

@@ -56,7 +56,7 @@ def test_cheb_conv(dev, K, weighted):
     _check(m, r, (x.to(dev),) + extra_g, (x,) + extra_r)
 
 
-@pytest.mark.parametrize('aggr', ['add', 'mean'])
+@pytest.mark.parametrize('aggr', ['add', 'mean', 'max'])
 def test_graph_conv(dev, aggr):
     from torch_geometric.nn import GraphConv
     n, E, fin, fout = 250, 2500, 16, 24
