@@ -184,7 +184,9 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
  * sub_rot rotates the work order: the launch starts at sub-item sub_rot (slot
  * sub_rot * Ts) and wraps around, so that ranks writing to each other begin at
  * different row blocks and no peer receives from everybody at once; the result
- * does not depend on it. */
+ * does not depend on it.  max_ctas > 0 caps the persistent grid (the chunked
+ * pipeline of dist/sliced.py leaves some SMs to the routed transform that runs
+ * concurrently on another stream); 0: every SM. */
 int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, int64_t ldx,
                                          int64_t F, const int32_t* rowptr,
                                          const int32_t* idx_flagged, const float* edge_w,
@@ -192,7 +194,8 @@ int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, i
                                          const int32_t* nz_rows, const int32_t* sub_info,
                                          int32_t Ts, int64_t n_sub, void* const* out_tab,
                                          int64_t blk_rows, int64_t sub_rot, int64_t ldo,
-                                         void* ws, size_t ws_bytes, pygb_stream_t s);
+                                         int64_t max_ctas, void* ws, size_t ws_bytes,
+                                         pygb_stream_t s);
 
 /* Same walk with a per-(edge, head) weight: out[i,h,:] = sum_p
  * head_w[wp(p)*H + h] * x[idx[p],h,:], wp(p) = wperm ? wperm[p] : p — GAT's
@@ -396,12 +399,15 @@ int pygb_gemm_xtg(const float* X, int64_t ldx, const float* G, int64_t ldg, int6
  *   dst_tab[q * n_dup + d] + (dst_row0 + r) * ldd + c      for every d < n_dup,
  * dst_tab a DEVICE array of (N/Fc) * n_dup base pointers, local or peer-GPU memory
  * (pygb_peer_open): the tiles leave over NVLink while the main loop of the next
- * tile runs.  Fc and ldd multiples of 4, bases 16-byte aligned, n_dup <= 4. */
+ * tile runs.  Fc and ldd multiples of 4, bases 16-byte aligned, n_dup <= 4.
+ * max_ctas > 0 caps the persistent grid: the epilogue is NVLink-bound, a fraction of
+ * the SMs saturates the links and the rest stay free for a concurrent aggregation. */
 int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane,
                         int64_t M, int64_t K, const float* W, int64_t ldw, int64_t N,
                         const float* bias, int relu,
                         float* const* dst_tab, int64_t Fc, int32_t n_dup, int64_t dst_row0,
-                        int64_t ldd, int passes, void* ws, size_t ws_bytes, pygb_stream_t s);
+                        int64_t ldd, int passes, int64_t max_ctas, void* ws, size_t ws_bytes,
+                        pygb_stream_t s);
 
 /* ---- multi-GPU: peer memory and the row -> column redistribution ------------ */
 

@@ -181,6 +181,13 @@ struct GemmParams {
   int stages;     // 2..kMaxStages
   int tmem_cols;  // power of two >= acc_bufs * MH * BN
   int acc_bufs;   // accumulator buffers in TMEM (2: the epilogue overlaps the next main loop)
+  int split_acc;  // 3xTF32: the correction terms Al.Wh + Ah.Wl accumulate in their own TMEM
+                  // columns (added in the epilogue).  The tensor core's fp32 accumulator
+                  // truncates (~2^-25.5 relative per accumulation, a bias towards zero that grows
+                  // with K); keeping the 2^-11-sized corrections out of the main chain cuts the
+                  // number of truncating updates of the large partial sum by 3 (K = 602:
+                  // 8.6e-6 -> ~3e-6 of the largest entry against fp64).  Used when TMEM has room
+                  // (2 buffers x 2 x MH*BN <= 512 columns).
   int m_tiles, n_tiles;
   // routed output (row layout -> column layout fused into the epilogue): column block
   // q = col / c_fc of row r goes to c_tab[q * c_dup + d] + (c_row0 + r) * c_ldd + col % c_fc
@@ -232,8 +239,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 
   const int nk = (P.K + kBK - 1) / kBK;
   const int n_tiles_total = P.m_tiles * P.n_tiles;
-  const int acc_cols = MH * BN;                   // TMEM columns of one accumulator buffer
-  const int nbuf = P.acc_bufs;                    // 2, or 1 when 2 * acc_cols > 512
+  const int acc_cols = MH * BN;                   // TMEM columns of one accumulator
+  const int acc_stride = acc_cols * (P.split_acc ? 2 : 1);   // columns of one buffer
+  const bool split_acc = PASSES == 3 && P.split_acc != 0;
+  const int nbuf = P.acc_bufs;                    // 2, or 1 when 2 * acc_stride > 512
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) {
@@ -299,7 +308,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         const int buf = tl % nbuf;
         mbar_wait(acc_empty(buf), ((uint32_t)(tl / nbuf) & 1u) ^ 1u);  // epilogue drained this buffer
         tcgen05_fence_after();
-        const uint32_t dcol = tmem_d + (uint32_t)(buf * acc_cols);
+        const uint32_t dcol = tmem_d + (uint32_t)(buf * acc_stride);
         for (int kt = 0; kt < nk; ++kt, ++it) {
           const int s = it % S;
           const uint32_t ph = (uint32_t)(it / S) & 1u;
@@ -319,8 +328,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
               if (KIND == 1) mma_f16(dc, dah + 2u * k, dbh + 2u * k, idesc, acc);
               else mma_tf32(dc, dah + 2u * k, dbh + 2u * k, idesc, acc);
               if (PASSES == 3) {
-                mma_tf32(dc, dal + 2u * k, dbh + 2u * k, idesc, 1u);
-                mma_tf32(dc, dah + 2u * k, dbl + 2u * k, idesc, 1u);
+                const uint32_t dcc = split_acc ? dc + (uint32_t)acc_cols : dc;
+                mma_tf32(dcc, dal + 2u * k, dbh + 2u * k, idesc, split_acc ? acc : 1u);
+                mma_tf32(dcc, dah + 2u * k, dbl + 2u * k, idesc, 1u);
               }
             }
           }
@@ -382,7 +392,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       tcgen05_fence_after();
       for (int h = 0; h < MH; ++h) {
       const int row0 = m0 + h * kBM + q * 32;
-      const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * acc_cols + h * BN);
+      const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * acc_stride + h * BN);
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t r[32];
         if (c0 + 32 <= BN) {
@@ -393,6 +403,20 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           for (int j = 16; j < 32; ++j) r[j] = 0u;
         }
         tmem_ld_wait();
+        if (split_acc) {  // main + corrections, one round-to-nearest fp32 add
+          uint32_t r2[32];
+          if (c0 + 32 <= BN) {
+            tmem_ld32(tbase + (uint32_t)(acc_cols + c0), r2);
+          } else {
+            tmem_ld16(tbase + (uint32_t)(acc_cols + c0), r2);
+#pragma unroll
+            for (int j = 16; j < 32; ++j) r2[j] = 0u;
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+        }
 #pragma unroll
         for (int j = 0; j < 32; j += 4)
           asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(
@@ -887,6 +911,7 @@ size_t pygb_gemm_weight_workspace(int64_t K, int64_t N) {
 struct GemmRoute {
   float* const* tab;
   int64_t fc, dup, row0, ldd;
+  int64_t max_ctas;   // > 0: cap of the persistent grid (NVLink-bound epilogue: a few SMs are enough)
 };
 
 static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a_plane, int64_t M,
@@ -964,9 +989,12 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
     }
   }
   const int acc_cols = mh * P.BN;
-  P.acc_bufs = 2 * acc_cols <= 512 ? 2 : 1;
+  P.split_acc = (passes == 3 && 4 * acc_cols <= 512) ? 1 : 0;
+  if (const char* e = getenv("PYGB_GEMM_SPLIT_ACC")) P.split_acc = P.split_acc && atoi(e) != 0;
+  const int acc_stride = acc_cols * (P.split_acc ? 2 : 1);
+  P.acc_bufs = 2 * acc_stride <= 512 ? 2 : 1;
   int tc = 32;
-  while (tc < P.acc_bufs * acc_cols) tc <<= 1;
+  while (tc < P.acc_bufs * acc_stride) tc <<= 1;
   P.tmem_cols = tc;
   P.m_tiles = (int)ceil_div(M, mh * kBM);
   const size_t b_bytes = (size_t)P.BN * bk * 4;
@@ -991,7 +1019,9 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
   if (rc) return rc;
 
   const int64_t tiles = (int64_t)P.m_tiles * P.n_tiles;
-  dim3 grid((unsigned)(tiles < sms ? tiles : sms));
+  int64_t ctas = tiles < sms ? tiles : sms;
+  if (route && route->max_ctas > 0 && ctas > route->max_ctas) ctas = route->max_ctas;
+  dim3 grid((unsigned)ctas);
 #define PYGB_GEMM_LAUNCH(PS, MHV, BKV)                                                         \
   do {                                                                                         \
     PYGB_CUDA(cudaFuncSetAttribute(gemm_tf32_kernel<PS, MHV, BKV>,                             \
@@ -1131,6 +1161,7 @@ int pygb_gemm_xw_bf16(const void* A, int64_t lda, int64_t M, int64_t K, const vo
   int sms = 148, dev = 0;
   PYGB_CUDA(cudaGetDevice(&dev));
   PYGB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  P.split_acc = 0;
   P.acc_bufs = 2 * P.BN <= 512 ? 2 : 1;
   int tc = 32;
   while (tc < P.acc_bufs * P.BN) tc <<= 1;
@@ -1175,12 +1206,13 @@ int pygb_gemm_xw_routed(const float* A, int64_t lda, int64_t a_slices, int64_t a
                         int64_t K, const float* W, int64_t ldw, int64_t N, const float* bias,
                         int relu,
                         float* const* dst_tab, int64_t Fc, int32_t n_dup, int64_t dst_row0,
-                        int64_t ldd, int passes, void* ws, size_t ws_bytes, pygb_stream_t s) {
+                        int64_t ldd, int passes, int64_t max_ctas, void* ws, size_t ws_bytes,
+                        pygb_stream_t s) {
   PYGB_REQUIRE(dst_tab && Fc > 0 && Fc % 4 == 0 && N % Fc == 0 && n_dup >= 1 && n_dup <= kMaxDup &&
                    dst_row0 >= 0 && ldd >= Fc && ldd % 4 == 0,
                "pygb_gemm_xw_routed: N must be a whole number of column blocks of Fc (multiple "
                "of 4) columns, 1 <= n_dup <= %d", kMaxDup);
-  GemmRoute r{dst_tab, Fc, n_dup, dst_row0, ldd};
+  GemmRoute r{dst_tab, Fc, n_dup, dst_row0, ldd, max_ctas};
   return gemm_xw_impl(A, lda, a_slices, a_plane, M, K, W, ldw, N, bias, relu, nullptr, N, &r,
                       passes, ws, ws_bytes, s);
 }

@@ -67,6 +67,7 @@ struct StreamParams {
   int blk_rows;
   unsigned blk_magic;  // floor(2^32 / blk_rows) + 1
   int sub_rot;         // first sub-item this launch starts at (work order rotation)
+  int max_ctas;        // > 0: cap of the persistent grid (leaves SMs to a concurrent kernel)
   int64_t out_off;  // bytes
 };
 
@@ -382,6 +383,7 @@ int launch_stream_k(const StreamParams& P, cudaStream_t st) {
   int64_t grid = (int64_t)sm_count() * ctas_per_sm;
   const int64_t need = ceil_div(n_items, kStreamWarps);
   if (grid > need) grid = need;
+  if (P.max_ctas > 0 && grid > P.max_ctas) grid = P.max_ctas;
   if (grid < 1) grid = 1;
   kern<<<(unsigned)grid, kStreamWarps * 32, C::CTA_B, st>>>(P);
   PYGB_LAUNCH_CHECK();
@@ -514,7 +516,7 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
                            const float* bias, int64_t n_rows, int64_t E, const int32_t* nz_rows,
                            const int32_t* sub_info, int32_t Ts, int64_t n_sub, void* out,
                            void* const* out_tab, int64_t blk_rows, int64_t sub_rot, int64_t ldo,
-                           void* ws, size_t ws_bytes, pygb_stream_t s) {
+                           int64_t max_ctas, void* ws, size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(reduce == PYGB_SUM || reduce == PYGB_MEAN,
                "pygb_seg_gather_reduce_stream: bad reduce %d", reduce);
   PYGB_REQUIRE(dtype == PYGB_F32 || dtype == PYGB_BF16,
@@ -566,6 +568,7 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
     P.blk_rows = (int)blk_rows;
     P.blk_magic = out_tab ? (unsigned)((1ull << 32) / (uint64_t)blk_rows + 1) : 0u;
     P.sub_rot = (int)sub_rot;
+    P.max_ctas = (int)(max_ctas > 0 && max_ctas < (1 << 30) ? max_ctas : 0);
     P.out_off = f0 * esz;
     P.ldo = ldo;
     P.sub_info = sub_info;
@@ -590,7 +593,7 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
                                   size_t ws_bytes, pygb_stream_t s) {
   PYGB_REQUIRE(out || n_rows == 0 || F == 0, "pygb_seg_gather_reduce_stream: null pointer");
   return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
-                         nz_rows, sub_info, Ts, n_sub, out, nullptr, 0, 0, ldo, ws, ws_bytes, s);
+                         nz_rows, sub_info, Ts, n_sub, out, nullptr, 0, 0, ldo, 0, ws, ws_bytes, s);
 }
 
 int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, int64_t ldx,
@@ -599,13 +602,14 @@ int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, i
                                          const float* bias, int64_t n_rows, int64_t E,
                                          const int32_t* nz_rows, const int32_t* sub_info,
                                          int32_t Ts, int64_t n_sub, void* const* out_tab,
-                                         int64_t blk_rows, int64_t sub_rot, int64_t ldo, void* ws,
-                                         size_t ws_bytes, pygb_stream_t s) {
+                                         int64_t blk_rows, int64_t sub_rot, int64_t ldo,
+                                         int64_t max_ctas, void* ws, size_t ws_bytes,
+                                         pygb_stream_t s) {
   PYGB_REQUIRE(out_tab || n_rows == 0 || F == 0,
                "pygb_seg_gather_reduce_stream_routed: null pointer table");
   return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
                          nz_rows, sub_info, Ts, n_sub, nullptr, out_tab, blk_rows, sub_rot, ldo,
-                         ws, ws_bytes, s);
+                         max_ctas, ws, ws_bytes, s);
 }
 
 }  // extern "C"

@@ -45,7 +45,7 @@ SIGNATURES = {
     'pygb_seg_gather_reduce_stream': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P, _I,
                                            _L, _P, _L, _P, _Z, _P]),
     'pygb_seg_gather_reduce_stream_routed': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P,
-                                                  _I, _L, _P, _L, _L, _L, _P, _Z, _P]),
+                                                  _I, _L, _P, _L, _L, _L, _L, _P, _Z, _P]),
     'pygb_peer_alloc': (_I, [_Z, _P]),
     'pygb_peer_free': (_I, [_P]),
     'pygb_peer_export': (_I, [_P, _P, _Z]),
@@ -54,7 +54,7 @@ SIGNATURES = {
     'pygb_peer_barrier': (_I, [_P, _I, _I, _L, _L, _P]),
     'pygb_cols_scatter': (_I, [_I, _P, _L, _L, _L, _I, _I, _P, _L, _L, _I, _P]),
     'pygb_gemm_xw_routed': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _L, _L, _I,
-                                 _P, _Z, _P]),
+                                 _L, _P, _Z, _P]),
     'pygb_seg_gather_reduce_heads': (_I, [_I, _P, _L, _I, _I, _P, _P, _P, _P, _P, _L, _P, _L, _P]),
     'pygb_gather_rows': (_I, [_I, _P, _L, _L, _P, _L, _P, _L, _P]),
     'pygb_edge_dot': (_I, [_I, _P, _L, _P, _L, _L, _P, _P, _P, _L, _L, _P, _P]),

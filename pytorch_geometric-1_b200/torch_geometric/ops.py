@@ -124,7 +124,7 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
 
 
 def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, reduce='sum',
-                                 start_row=0):
+                                 start_row=0, max_ctas=0):
     """The streaming fused gather-reduce with a routed output: row ``r`` of the
     result is stored at ``out_tab[r // blk_rows] + (r % blk_rows) * ldo`` (element
     units of ``x.dtype``) — ``out_tab`` is an int64 CUDA tensor of base addresses,
@@ -161,7 +161,7 @@ def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, re
              nat.MEAN if reduce == 'mean' else nat.SUM, dt, nat.ptr(x2), _ld(x2), F,
              nat.ptr(csr.rowptr), nat.ptr(idxf), nat.ptr(_f32(w_csr)), nat.ptr(_f32(bias)),
              csr.n_rows, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub, nat.ptr(out_tab),
-             int(blk_rows), int(sub_rot), int(ldo), nat.ptr(ws), ws_bytes)
+             int(blk_rows), int(sub_rot), int(ldo), int(max_ctas), nat.ptr(ws), ws_bytes)
 
 
 def cols_scatter_raw(src, Fc, n_parts, dst_tab, dst_row0, ldd, relu=False, n_dup=1):
@@ -177,7 +177,7 @@ def cols_scatter_raw(src, Fc, n_parts, dst_tab, dst_row0, ldd, relu=False, n_dup
 
 
 def gemm_xw_routed_raw(x, w, bias, Fc, dst_tab, dst_row0, ldd, relu=False, n_dup=1, passes=None,
-                       rows=None):
+                       rows=None, max_ctas=0):
     """``relu?(x @ w + bias)`` with the result's column blocks of ``Fc`` columns stored
     through ``dst_tab`` (pygb_gemm_xw_routed): the row -> column layout change of the
     feature-sliced multi-GPU forward fused into the GEMM epilogue.  ``x`` as in
@@ -193,8 +193,8 @@ def gemm_xw_routed_raw(x, w, bias, Fc, dst_tab, dst_row0, ldd, relu=False, n_dup
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     nat.call('pygb_gemm_xw_routed', dev, a_ptr, lda, a_slices, a_plane, M, K, nat.ptr(w),
              w.stride(0), N, nat.ptr(_f32(bias)), int(bool(relu)), nat.ptr(dst_tab), int(Fc),
-             int(n_dup), int(dst_row0), int(ldd), int(passes or GEMM_PASSES), nat.ptr(ws),
-             ws_bytes)
+             int(n_dup), int(dst_row0), int(ldd), int(passes or GEMM_PASSES), int(max_ctas),
+             nat.ptr(ws), ws_bytes)
 
 
 def gather_rows_raw(x, index):

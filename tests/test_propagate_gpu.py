@@ -185,7 +185,10 @@ def test_gcn_bf16(dev):
     _sync(conv, ref)
     out = conv.to(torch.bfloat16)(x.to(dev).to(torch.bfloat16), ei.to(dev))
     assert out.dtype == torch.bfloat16
-    assert_close(out.float(), ref(x, ei), 1e-2)
+    # inputs, weights and the result are rounded to bf16 (2^-8 relative each): an element that
+    # is a cancelling sum inherits that error relative to its largest addend -> absolute floor
+    # of one bf16 ulp of the largest entry
+    assert_close(out.float(), ref(x, ei), 1e-2, floor=4e-3)
 
 
 @pytest.mark.parametrize('H,C,concat', [(8, 8, True), (1, 16, True), (4, 7, False), (6, 121, False),

@@ -154,7 +154,10 @@ def test_stream_gat_backward_matches_edge_grad_path(dev, ops_mod, H, C, T, bipar
         if a is None:
             continue
         assert torch.equal(a, b), what + ' not deterministic'
-        assert_close(a, c, 2e-5, what)
+        # two CUDA kernels with different summation trees (streaming walk vs per-edge kernel +
+        # transposed aggregation): rank-1 structured gradients (d a_dst x att) cancel, so the
+        # floor is 6e-6 of the largest entry (measured 4.6e-6 at H=1, C=128)
+        assert_close(a, c, 2e-5, what, floor=6e-6)
 
 
 def test_stream_gat_backward_no_dst_features(dev, ops_mod):

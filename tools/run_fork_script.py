@@ -138,12 +138,16 @@ def run(script, argv=(), workdir=None):
 
 
 def main():
+    # hand-parsed so that everything after `--` reaches the script untouched
+    argv = sys.argv[1:]
+    rest = []
+    if '--' in argv:
+        k = argv.index('--')
+        argv, rest = argv[:k], argv[k + 1:]
     ap = argparse.ArgumentParser(description=__doc__.split('\n')[0])
     ap.add_argument('script', help='path relative to the fork root, e.g. examples/gcn.py')
     ap.add_argument('--workdir', default=None)
-    ap.add_argument('rest', nargs=argparse.REMAINDER, help='-- arguments of the script')
-    args = ap.parse_args()
-    rest = args.rest[1:] if args.rest[:1] == ['--'] else args.rest
+    args = ap.parse_args(argv)
     run(args.script, rest, args.workdir)
     print('[run_fork_script] finished OK')
 
