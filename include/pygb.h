@@ -184,9 +184,9 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
  * sub_rot rotates the work order: the launch starts at sub-item sub_rot (slot
  * sub_rot * Ts) and wraps around, so that ranks writing to each other begin at
  * different row blocks and no peer receives from everybody at once; the result
- * does not depend on it.  max_ctas > 0 caps the persistent grid (the chunked
- * pipeline of dist/sliced.py leaves some SMs to the routed transform that runs
- * concurrently on another stream); 0: every SM. */
+ * does not depend on it.  max_ctas > 0 caps the persistent grid, max_ctas < 0
+ * leaves |max_ctas| SMs free (the chunked pipeline of dist/sliced.py runs the routed
+ * transform concurrently on another stream); 0: every SM. */
 int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, int64_t ldx,
                                          int64_t F, const int32_t* rowptr,
                                          const int32_t* idx_flagged, const float* edge_w,

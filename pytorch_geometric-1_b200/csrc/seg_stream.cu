@@ -67,7 +67,8 @@ struct StreamParams {
   int blk_rows;
   unsigned blk_magic;  // floor(2^32 / blk_rows) + 1
   int sub_rot;         // first sub-item this launch starts at (work order rotation)
-  int max_ctas;        // > 0: cap of the persistent grid (leaves SMs to a concurrent kernel)
+  int max_ctas;        // > 0: cap of the persistent grid; < 0: leave |max_ctas| SMs to a
+                       // concurrent kernel (grid = (SMs + max_ctas) x resident CTAs per SM)
   int64_t out_off;  // bytes
 };
 
@@ -384,6 +385,11 @@ int launch_stream_k(const StreamParams& P, cudaStream_t st) {
   const int64_t need = ceil_div(n_items, kStreamWarps);
   if (grid > need) grid = need;
   if (P.max_ctas > 0 && grid > P.max_ctas) grid = P.max_ctas;
+  if (P.max_ctas < 0) {
+    int64_t sms_left = (int64_t)sm_count() + P.max_ctas;
+    if (sms_left < 1) sms_left = 1;
+    if (grid > sms_left * ctas_per_sm) grid = sms_left * ctas_per_sm;
+  }
   if (grid < 1) grid = 1;
   kern<<<(unsigned)grid, kStreamWarps * 32, C::CTA_B, st>>>(P);
   PYGB_LAUNCH_CHECK();
@@ -568,7 +574,7 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
     P.blk_rows = (int)blk_rows;
     P.blk_magic = out_tab ? (unsigned)((1ull << 32) / (uint64_t)blk_rows + 1) : 0u;
     P.sub_rot = (int)sub_rot;
-    P.max_ctas = (int)(max_ctas > 0 && max_ctas < (1 << 30) ? max_ctas : 0);
+    P.max_ctas = (int)(max_ctas > -(1 << 20) && max_ctas < (1 << 30) ? max_ctas : 0);
     P.out_off = f0 * esz;
     P.ldo = ldo;
     P.sub_info = sub_info;

@@ -51,14 +51,16 @@ class SlicePlan(object):
     Row block ``q`` (``blk`` rows) is owned by rank ``q``; row group ``rg`` is the union
     of the blocks of its ranks."""
 
-    def __init__(self, num_nodes, world_size, rank, row_groups=1):
+    def __init__(self, num_nodes, world_size, rank, row_groups=1, blk_align=1):
         self.num_nodes, self.world_size, self.rank = int(num_nodes), int(world_size), int(rank)
         self.Gr = int(row_groups)
         if self.Gr < 1 or self.world_size % self.Gr:
             raise ValueError('row_groups must divide the world size')
         self.Gc = self.world_size // self.Gr
         self.rg, self.cg = divmod(self.rank, self.Gc)
-        self.blk = max(_ceil_div(self.num_nodes, self.world_size), 2)
+        # blk_align: row blocks that split into equal row chunks (the chunked pipeline below)
+        self.blk = _ceil_div(max(_ceil_div(self.num_nodes, self.world_size), 2),
+                             int(blk_align)) * int(blk_align)
         self.n_padded = self.blk * self.world_size
         self.lo = min(self.rank * self.blk, self.num_nodes)
         self.hi = min(self.lo + self.blk, self.num_nodes)
@@ -233,6 +235,8 @@ class PeerTransport(object):
         self.slice_major = True
         self._tabs = {}
         self._flag = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self._side = None               # high-priority stream of the chunked pipeline
+        self.gemm_ctas = 32             # SMs given to the routed transform while it overlaps
         nat.load()
 
     # ---- arena ---------------------------------------------------------------------
@@ -393,6 +397,70 @@ class PeerTransport(object):
         self.fence()
         return self._view(self._c_off, p.n_padded, Fc)
 
+    def in_arena(self, t):
+        return (self._base is not None and self._mem is not None
+                and self._base <= t.data_ptr() < self._base + self._mem.numel())
+
+    def aggregate_transform_pipelined(self, graph, cols, F_agg, w, bias, F_out, relu):
+        """``relu?((A cols) @ w + bias)`` -> column layout, as a pipeline over row chunks.
+
+        The aggregation of row chunk c stores straight into the row buffers of the owners (as
+        in ``aggregate_to_rows``); after a fence the owner's routed transform of chunk c runs
+        on a second, high-priority stream, with a capped grid, while the aggregation of chunk
+        c+1 runs on the SMs left to it.  The transform's epilogue is NVLink-bound (every rank
+        receives its column slice of all N rows: 548 MB at P = 8) and the aggregation is
+        HBM-bound, so the two overlap instead of adding up.  Results are
+        bit-identical to the unchunked path: every row is summed in the same slot order."""
+        from .. import ops
+        self._check(cols)
+        p = self.plan
+        C = graph.chunks
+        blk_c = p.blk // C
+        Fpa, Fca = p.widths(F_agg, 4)
+        Fpo, Fco = p.widths(F_out, 4)
+        self.ensure(max(Fpa, Fpo))
+        self._flip ^= 1
+        off = self._r_off[self._flip]
+        sliced = self.slice_major and Fca % 32 == 0 and p.Gc > 1
+        ldo = Fca if sliced else Fpa
+        main = torch.cuda.current_stream(self.device)
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.device, priority=-1)
+        side = self._side
+        cols_tab = self._cols_table()
+        rows_all = self._view(off, p.blk, Fpa)
+        if sliced:
+            rows_all = rows_all.view(p.Gc, p.blk, Fca)
+        rot = ((p.cg + 1) % p.Gc) * blk_c if self.rotate else 0
+        for c in range(C):
+            adj_c, w_c = graph.chunk(c)
+            if sliced:
+                base = off + (p.cg * p.blk + c * blk_c) * Fca * 4
+            else:
+                base = off + c * blk_c * Fpa * 4 + p.cg * Fca * 4
+            tab = self._table(('rc', self._flip, Fca, c, C),
+                              [self._peer[p.rg * p.Gc + j] + base for j in range(p.Gc)])
+            ops.seg_gather_reduce_routed_raw(cols[:, :Fca], adj_c.dst, w_c, None, tab, blk_c, ldo,
+                                             start_row=rot,
+                                             max_ctas=-self.gemm_ctas if c > 0 else 0)
+            self.fence()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            n_c = min(max(p.n_local - c * blk_c, 0), blk_c)
+            with torch.cuda.stream(side):
+                side.wait_event(ev)
+                if n_c > 0:
+                    a = rows_all[:, c * blk_c:c * blk_c + n_c] if sliced else \
+                        rows_all[c * blk_c:c * blk_c + n_c]
+                    ops.gemm_xw_routed_raw(a, w, bias, Fco, cols_tab, p.lo + c * blk_c, Fco, relu,
+                                           p.Gr, rows=n_c,
+                                           max_ctas=self.gemm_ctas if c + 1 < C else 0)
+        main.wait_stream(side)
+        self.bytes_sent_total += (p.Gc - 1) * p.blk * Fca * 4
+        self._sent_cols(Fco)
+        self.fence()
+        return self._view(self._c_off, p.n_padded, Fco)
+
     def rows_to_cols(self, rows, F, relu=False):
         from .. import ops
         self._check(rows)
@@ -436,8 +504,11 @@ class SlicedGraph(object):
 
     def __init__(self, edge_index, norm, num_nodes, rank, world_size, group=None, i=1,
                  transport='peer', build_adj=True, row_groups=1, fence_mode='nccl'):
-        self.plan = p = SlicePlan(num_nodes, world_size, rank, row_groups)
+        self.plan = p = SlicePlan(num_nodes, world_size, rank, row_groups,
+                                  blk_align=8 if transport == 'peer' else 1)
         self.i = i
+        self.chunks = 1
+        self._chunk_graphs = {}
         self.device = edge_index.device
         if p.Gr > 1:                                   # in-edges of the row group, renumbered
             t = edge_index[i]
@@ -461,6 +532,43 @@ class SlicedGraph(object):
         else:
             raise ValueError("transport must be 'peer' or 'collective'")
         self._bufs = {}
+
+    def set_chunks(self, chunks):
+        """Row chunks of the pipelined aggregate -> transform step (peer transport; 1 = off).
+        Must divide the row block (a multiple of 8)."""
+        chunks = max(int(chunks), 1)
+        if chunks > 1 and (self.plan.blk % chunks or not getattr(self.transport, 'fused', False)):
+            raise ValueError('chunks must divide the row block ({}) and need the peer '
+                             'transport'.format(self.plan.blk))
+        if chunks != self.chunks:
+            self._chunk_graphs = {}
+        self.chunks = chunks
+        for c in range(chunks if chunks > 1 else 0):
+            self.chunk(c)                           # sort the sub-graphs now, not in a timed step
+
+    def chunk(self, c):
+        """(Adj, w_csr) of row chunk ``c``: the in-edges of rows ``[c*blk_c, (c+1)*blk_c)`` of
+        EVERY row block of the group, destinations renumbered ``block*blk_c + offset`` — the
+        stable sort keeps each row's edge order, so sums equal the whole graph's bit for bit."""
+        hit = self._chunk_graphs.get(c)
+        if hit is not None:
+            return hit
+        from ..graph import Adj
+        p, i = self.plan, self.i
+        blk_c = p.blk // self.chunks
+        t = self.edge_index[i]
+        r = t % p.blk
+        mask = (r // blk_c) == c
+        ei = self.edge_index[:, mask].clone()
+        ei[i] = (t[mask] // p.blk) * blk_c + (r[mask] % blk_c)
+        size = [0, 0]
+        size[i], size[1 - i] = p.Gc * blk_c, p.num_nodes
+        adj = Adj(ei, i, size)
+        w = None if self.norm is None else adj.permuted(self.norm[mask].float().contiguous(), 'dst')
+        adj.dst.items(None)
+        adj.dst.flagged('col')
+        self._chunk_graphs[c] = (adj, w)
+        return adj, w
 
     def local_rows(self, x_global):
         return x_global[self.plan.lo:self.plan.hi]
@@ -548,7 +656,30 @@ def sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols', aggregate=_
     # re-allocate it under a live row buffer)
     tr.prepare(max([p.widths(f, esz)[0] for w, _ in layers for f in w.shape] or [0]))
     state, kind = x, x_layout
+    skip = False
     for n_op, op in enumerate(ops_seq):
+        if skip:
+            skip = False
+            continue
+        nxt = ops_seq[n_op + 1] if n_op + 1 < len(ops_seq) else None
+        nxt2 = ops_seq[n_op + 2] if n_op + 2 < len(ops_seq) else None
+        if (op[0] == 'agg' and getattr(graph, 'chunks', 1) > 1 and getattr(tr, 'fused', False)
+                and aggregate is _native_aggregate and transform is _native_transform
+                and kind == 'cols' and op[2] is None and not op[3]
+                and nxt is not None and nxt[0] == 'gemm' and nxt2 is not None and nxt2[0] == 'agg'
+                and state.dtype == torch.float32 and not tr.in_arena(state)):
+            # aggregate -> transform -> (next aggregation): pipelined over row chunks
+            _, F, _, _ = op
+            _, k, w, b, act = nxt
+            fout = w.size(1)
+            fpa, _ = p.widths(F, esz)
+            fpo, _ = p.widths(fout, esz)
+            wp = graph.padded(('w', k), w, fpa, fpo)
+            bp = graph.padded(('b', k), b, 0, fpo)
+            state = tr.aggregate_transform_pipelined(graph, state, F, wp, bp, fout, act)
+            kind = 'cols'
+            skip = True
+            continue
         if op[0] == 'agg':
             _, F, b, act = op
             if kind == 'rows':

@@ -50,10 +50,59 @@ class GATConv(MessagePassing):
         glorot(self.att)
         zeros(self.bias)
 
+    def _fusable(self, x):
+        cls = type(self)
+        if (cls.message is not GATConv.message or cls.update is not GATConv.update
+                or self.node_dim != 0 or (self.training and self.dropout > 0)):
+            return False
+        xs = x if torch.is_tensor(x) else (x[0] if self.flow == 'source_to_target' else x[1])
+        return (torch.is_tensor(xs) and xs.is_cuda and xs.dim() == 2
+                and xs.dtype in (torch.float32, torch.bfloat16))
+
+    def _forward_padded(self, x, edge_index, size, Cp):
+        """Fused route for head widths the streaming kernels do not take as they are (the fork
+        builds ``GATConv(width[i], width[i+1])`` with ``heads=1`` and arbitrary widths,
+        ConvexPruning.py:204-214): every head is zero-padded to ``Cp`` channels — in the WEIGHT,
+        so X·W comes out of the GEMM already in the padded layout — and the result is sliced
+        back.  Exact (padded channels contribute 0 everywhere); update() is applied here."""
+        H, C = self.heads, self.out_channels
+        fin = self.weight.size(0)
+        w = F.pad(self.weight.view(fin, H, C), (0, Cp - C)).reshape(fin, H * Cp)
+        a = self.att.view(1, H, 2, C)
+        att = F.pad(a, (0, Cp - C)).reshape(1, H, 2 * Cp)
+        i, j = (0, 1) if self.flow == 'target_to_source' else (1, 0)
+        if torch.is_tensor(x):
+            xs = xd = ops.linear(x, w)
+            n_src = n_dst = x.size(0)
+        else:
+            xs = ops.linear(x[j], w)
+            xd = None if x[i] is None else ops.linear(x[i], w)
+            n_src = xs.size(0)
+            n_dst = xd.size(0) if xd is not None else (size[i] if size is not None else n_src)
+        if size is not None:
+            if size[j] is not None:
+                n_src = size[j]
+            if size[i] is not None:
+                n_dst = size[i]
+        sz = [0, 0]
+        sz[i], sz[j] = n_dst, n_src
+        adj = adj_for(edge_index, i, sz)
+        out = ops.gat_propagate(xs, xd, att, None, adj, H, Cp, self.negative_slope)
+        out = out.view(-1, H, Cp)[:, :, :C]
+        out = out.reshape(-1, H * C) if self.concat else out.mean(dim=1)
+        return out + self.bias if self.bias is not None else out
+
     def forward(self, x, edge_index, size=None):
         """"""
         if size is None and torch.is_tensor(x):
             edge_index = self._with_self_loops(edge_index, x.size(self.node_dim))
+
+        if self._fusable(x):
+            esz = 4 if (x if torch.is_tensor(x) else [t for t in x if t is not None][0]).dtype \
+                == torch.float32 else 2
+            Cp = ops.gat_pad_channels(self.out_channels, esz)
+            if Cp != self.out_channels and Cp * esz <= 2048:
+                return self._forward_padded(x, edge_index, size, Cp)
 
         if torch.is_tensor(x):
             x = ops.linear(x, self.weight)

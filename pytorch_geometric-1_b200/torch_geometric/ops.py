@@ -563,11 +563,41 @@ class _GATFused(torch.autograd.Function):
         return d_xs, d_xd, d_att, d_bias, None, None, None, None, None
 
 
+def gat_pad_channels(C, itemsize=4):
+    """Channels per head the streaming GAT kernels want: a power of two in [4, 128] (forward and
+    both backward walks stream), else the next multiple of the 16-byte vector (forward streams,
+    backward uses the two-pass kernels).  Zero padding is exact: padded channels add 0 to every
+    logit and produce 0 outputs."""
+    vec = 16 // itemsize
+    if C <= 128:
+        cp = max(vec, 4)
+        while cp < C:
+            cp *= 2
+        return cp
+    return (C + vec - 1) // vec * vec
+
+
 def gat_propagate(x_src, x_dst, att, bias, adj, H, C, slope):
     """Fused GATConv message+softmax+aggregate (A.10).  ``x_dst`` is ``x_src``
-    itself (ordinary graphs), another tensor (bipartite) or None (x_i = None)."""
+    itself (ordinary graphs), another tensor (bipartite) or None (x_i = None).
+
+    Heads are independent, so wide layers (H*C beyond the 2 KB a lane group stages per row,
+    e.g. examples/ppi.py:22 GATConv(.., 256, heads=4)) run as one launch per group of heads on
+    column views of the same matrices — the streaming kernels instead of the two-pass ones."""
     same = x_dst is x_src
-    return _GATFused.apply(x_src, None if same else x_dst, att, bias, adj, H, C, slope, same)
+    per = max(1, 512 // max(C, 1)) if x_src.dtype == torch.float32 else max(1, 1024 // max(C, 1))
+    if H <= per or C * x_src.element_size() > 2048 or x_src.dim() != 2 or not STREAM:
+        return _GATFused.apply(x_src, None if same else x_dst, att, bias, adj, H, C, slope, same)
+    outs = []
+    att3 = att.reshape(1, H, 2 * C)
+    for h0 in range(0, H, per):
+        h1 = min(h0 + per, H)
+        xs = x_src[:, h0 * C:h1 * C]
+        xd = xs if same else (None if x_dst is None else x_dst[:, h0 * C:h1 * C])
+        b = None if bias is None else bias[h0 * C:h1 * C]
+        outs.append(_GATFused.apply(xs, None if same else xd, att3[:, h0:h1], b, adj, h1 - h0, C,
+                                    slope, same))
+    return torch.cat(outs, dim=1)
 
 
 # --------------------------------------------------------------------------

@@ -89,7 +89,7 @@ def test_dist_gcn_two_gpus_nccl():
 
 
 # ---- feature-sliced layout ---------------------------------------------------------
-def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence='flags'):
+def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence='flags', chunks=1):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for p in (root, os.path.join(root, 'pytorch_geometric-1_b200'), os.path.join(root, 'tests')):
@@ -119,6 +119,20 @@ def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence=
         lay = [(w.to(dev), b.to(dev)) for w, b in layers]
         for _ in range(3):                    # buffer reuse across steps (double-buffered rows)
             out_local = sliced_gcn_forward(g, xin, lay, x_layout=x_layout)
+        if chunks > 1:
+            # the chunked pipeline (aggregation of row chunk c+1 concurrent with the routed
+            # transform of chunk c on a second stream): same bits as the unchunked forward
+            plain = out_local.clone()
+            g.set_chunks(chunks)
+            from torch_geometric import _native as nat
+            for _ in range(3):
+                nat.event_log = []
+                out_local = sliced_gcn_forward(g, xin, lay, x_layout=x_layout)
+                names = [e[0] for e in nat.event_log]
+                nat.event_log = None
+            torch.cuda.synchronize()
+            assert torch.equal(out_local, plain), 'chunked pipeline changed the result'
+            assert names.count('pygb_gemm_xw_routed') == chunks + 1, names
         parts = [torch.zeros(pl.blk, 47, device=dev) for _ in range(world)]
         pad = torch.zeros(pl.blk, 47, device=dev)
         pad[:pl.n_local] = out_local
@@ -141,11 +155,12 @@ def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence=
         dist.destroy_process_group()
 
 
-def _run_sliced(world, transport, x_layout, row_groups=1, fence='flags'):
+def _run_sliced(world, transport, x_layout, row_groups=1, fence='flags', chunks=1):
     ctx = mp.get_context('spawn')
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_sliced_worker, args=(r, world, port, q, transport, x_layout, row_groups, fence))
+    procs = [ctx.Process(target=_sliced_worker,
+                         args=(r, world, port, q, transport, x_layout, row_groups, fence, chunks))
              for r in range(world)]
     for p in procs:
         p.start()
@@ -182,6 +197,60 @@ def test_sliced_gcn_four_gpus_two_row_groups(transport):
 def test_sliced_gcn_one_gpu(transport):
     """world_size 1: the same code path (routed stores into the rank's own arena)."""
     _run_sliced(1, transport, 'cols')
+
+
+@pytest.mark.parametrize('chunks', [2, 8])
+def test_sliced_gcn_one_gpu_chunked_pipeline(chunks):
+    """world_size 1, peer transport: the chunked aggregate -> transform pipeline (two streams,
+    capped grids) on the rank's own arena; bit-identical to the unchunked forward."""
+    _run_sliced(1, 'peer', 'cols', fence='nccl', chunks=chunks)
+
+
+@pytest.mark.parametrize('row_groups,chunks', [(1, 2), (1, 4), (2, 4)])
+def test_sliced_gcn_two_gpus_chunked_pipeline(row_groups, chunks):
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs')
+    _run_sliced(2, 'peer', 'cols', row_groups, fence='nccl', chunks=chunks)
+
+
+@pytest.mark.parametrize('chunks', [1, 4])
+def test_sliced_gcn_eight_gpus_two_by_four(chunks):
+    """The layout the driver's 8-GPU SCALE run uses: 2 row groups x 4 column slices, peer stores."""
+    if torch.cuda.device_count() < 8:
+        pytest.skip('needs eight GPUs')
+    _run_sliced(8, 'peer', 'cols', 2, fence='nccl', chunks=chunks)
+
+
+def test_routed_kernels_with_capped_grids(dev):
+    """max_ctas (persistent-grid caps used by the chunked pipeline) never changes a result."""
+    from util import skewed_graph
+    from torch_geometric import ops
+    from torch_geometric.graph import Adj
+    n, E, F, blk = 1200, 40000, 32, 300
+    ei = skewed_graph(n, E, 5).to(dev)
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(n, F, generator=g).to(dev)
+    w = torch.rand(E, generator=g).to(dev)
+    adj = Adj(ei, 1, (n, n))
+    outs = []
+    for cap in (0, 3, 40, -20, -147, -500):
+        bufs = [torch.full((blk, F), -7.0, device=dev) for _ in range(4)]
+        tab = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64).to(dev)
+        ops.seg_gather_reduce_routed_raw(x, adj.dst, adj.permuted(w, 'dst'), None, tab, blk, F,
+                                         max_ctas=cap)
+        outs.append(torch.cat(bufs))
+    assert all(torch.equal(o, outs[0]) for o in outs[1:])
+    M, K, N, Fc = 3000, 128, 256, 64
+    a = torch.randn(M, K, generator=g).to(dev)
+    wt = (torch.randn(K, N, generator=g) / K ** 0.5).to(dev)
+    res = []
+    for cap in (0, 1, 7, 32):
+        o = [torch.zeros(M, Fc, device=dev) for _ in range(N // Fc)]
+        tab = torch.tensor([t.data_ptr() for t in o], dtype=torch.int64).to(dev)
+        ops.gemm_xw_routed_raw(a, wt, None, Fc, tab, 0, Fc, relu=True, max_ctas=cap)
+        res.append(torch.cat(o, dim=1))
+    assert all(torch.equal(r, res[0]) for r in res[1:])
+    assert torch.equal(res[0], torch.relu(ops.gemm_xw_raw(a, wt)))
 
 
 def test_routed_gather_reduce_and_cols_scatter(dev):

@@ -176,3 +176,45 @@ def test_linear_3d_input_falls_back_to_matmul_semantics(dev):
     x = torch.randn(6, 5, 32, device=dev)
     w = torch.randn(32, 8, device=dev)
     assert_close(ops.linear(x, w), torch.matmul(x.double().cpu(), w.double().cpu()), 1e-5)
+
+
+@pytest.mark.parametrize('H,C,concat,bwd_stream', [
+    (1, 7, True, True), (1, 100, True, True), (1, 33, False, True), (6, 121, False, True),
+    (4, 256, True, False), (1, 300, True, False), (2, 130, True, False)])
+def test_gat_fork_shapes_run_on_streaming_kernels(dev, H, C, concat, bwd_stream):
+    """the fork builds ``GATConv(w_i, w_{i+1})`` with ``heads=1`` and
+    arbitrary widths (ConvexPruning.py:204-214); examples/ppi.py:22 uses 4 x 256.  Heads are
+    zero-padded to a streamable width (in the weight) and wide layers run per head group — the
+    native event log proves which entry points ran; values against the oracle."""
+    from torch_geometric import _native as nat
+    from torch_geometric.nn import GATConv
+    n, E, fin = 700, 9000, 24
+    ei = skewed_graph(n, E, H * C)
+    x = _feat(n, fin, 1)
+    conv = GATConv(fin, C, heads=H, concat=concat).to(dev)
+    ref = O.GATConv(fin, C, heads=H, concat=concat)
+    with torch.no_grad():
+        conv.bias.uniform_(-1, 1)
+    _sync(conv, ref)
+    a = x.clone().requires_grad_(True)
+    b = x.to(dev).requires_grad_(True)
+    nat.event_log = []
+    try:
+        rb = conv(b, ei.to(dev))
+        fwd_names = [e[0] for e in nat.event_log]
+        nat.event_log = []
+        g = torch.randn(rb.shape, generator=torch.Generator().manual_seed(3))
+        rb.backward(g.to(dev))
+        bwd_names = [e[0] for e in nat.event_log]
+    finally:
+        nat.event_log = None
+    assert 'pygb_gat_forward_stream' in fwd_names and 'pygb_gat_forward' not in fwd_names, fwd_names
+    if bwd_stream:
+        assert 'pygb_gat_backward_stream' in bwd_names and 'pygb_gat_edge_grad' not in bwd_names
+    ra = ref(a, ei)
+    assert_close(rb, ra, 2e-5, 'fwd', floor=5e-6)
+    ra.backward(g)
+    assert_close(b.grad, a.grad, 2e-4, 'dx')
+    assert_close(conv.weight.grad, ref.weight.grad, 2e-4, 'dW')
+    assert_close(conv.att.grad, ref.att.grad, 2e-4, 'datt')
+    assert_close(conv.bias.grad, ref.bias.grad, 2e-4, 'dbias')
