@@ -351,6 +351,24 @@ int pygb_gat_backward_stream(int mode, const float* row_feat, int64_t ld_row,
 int pygb_knn_graph(const float* x, int64_t ldx, int64_t n, int D, const int64_t* batch,
                    const int64_t* ptr, int k, int loop, int32_t* nbr, pygb_stream_t s);
 
+/* Farthest point sampling, `torch_cluster.fps` (examples/pointnet++.py:39): for every
+ * example b (points ptr[b]..ptr[b+1] of x [n, D] fp32), out[out_ptr[b] + t], t <
+ * out_ptr[b+1] - out_ptr[b], is the global index of the t-th sample: the first is
+ * ptr[b] + start[b] (start int64 [B], local index), every next one the point with the largest
+ * squared distance to the samples so far (ties to the lower index).  dmin: float scratch [n]. */
+int pygb_fps(const float* x, int64_t ldx, int64_t n, int D, const int64_t* ptr,
+             const int64_t* out_ptr, const int64_t* start, int64_t n_examples, float* dmin,
+             int64_t* out, pygb_stream_t s);
+
+/* Fixed-radius search, `torch_cluster.radius` (examples/pointnet++.py:40-41,46-48): for query
+ * q (y [n_y, D], example batch_y[q]) nbr[q, 0..count[q]) are the first max_num_neighbors
+ * points j of x in the same example (ptr_x) with |x_j - y_q|^2 <= r^2, in ascending j; the
+ * rest of the row is -1.  skip_same_index != 0 drops j == q (radius_graph without loops). */
+int pygb_radius(const float* x, int64_t ldx, const float* y, int64_t ldy, int D,
+                const int64_t* ptr_x, const int64_t* batch_y, int64_t n_y, float r,
+                int max_num_neighbors, int skip_same_index, int32_t* nbr, int32_t* count,
+                pygb_stream_t s);
+
 /* ---- K5: dense node-feature transform on the tensor cores ------------------ */
 
 /* C[M,N] = A[M,K] . W[K,N] (+ bias[N]), fp32 in / fp32 out — the

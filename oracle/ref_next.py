@@ -243,3 +243,56 @@ def topk_pooling(x, edge_index, batch, weight, ratio):
             if int(a) in pos and int(b) in pos]
     ei = torch.tensor(keep, dtype=torch.long).t().reshape(2, -1)
     return x[perm] * score[perm].view(-1, 1), ei, batch[perm], perm, score[perm]
+
+
+# ---- fps / radius / radius_graph (torch_cluster 1.5.x semantics, [UPSTREAM-RECALL]; ref
+# sites examples/pointnet++.py:39-41,46-48): plain Python loops ---------------------------
+def fps(x, batch=None, ratio=0.5, start=None):
+    """Farthest point sampling per example: ceil(ratio * n_b) indices in selection order;
+    the first sample is ``start[b]`` (local index, default 0), every next one the point with
+    the largest squared distance to the selected set, ties to the lower index."""
+    n = x.size(0)
+    batch = torch.zeros(n, dtype=torch.long) if batch is None else batch
+    xd = x.double()
+    out = []
+    for b in range(int(batch.max()) + 1 if n else 0):
+        ids = [i for i in range(n) if int(batch[i]) == b]
+        if not ids:
+            continue
+        m = -(-int(round(ratio * len(ids) * 1e6)) // 10 ** 6)
+        cur = ids[0 if start is None else int(start[b])]
+        dmin = {i: float('inf') for i in ids}
+        for _ in range(m):
+            out.append(cur)
+            for i in ids:
+                dmin[i] = min(dmin[i], float(((xd[i] - xd[cur]) ** 2).sum()))
+            cur = max(ids, key=lambda i: (dmin[i], -i))
+    return torch.tensor(out, dtype=torch.long)
+
+
+def radius(x, y, r, batch_x=None, batch_y=None, max_num_neighbors=32):
+    """[2, E]: row 0 = y index, row 1 = x index; per y the first max_num_neighbors x of the
+    same example with |x - y| <= r, in ascending x index."""
+    batch_x = torch.zeros(x.size(0), dtype=torch.long) if batch_x is None else batch_x
+    batch_y = torch.zeros(y.size(0), dtype=torch.long) if batch_y is None else batch_y
+    xd, yd = x.double(), y.double()
+    rows, cols = [], []
+    for q in range(y.size(0)):
+        found = 0
+        for j in range(x.size(0)):
+            if int(batch_x[j]) != int(batch_y[q]) or found >= max_num_neighbors:
+                continue
+            if float(((xd[j] - yd[q]) ** 2).sum()) <= r * r:
+                rows.append(q)
+                cols.append(j)
+                found += 1
+    return torch.tensor([rows, cols], dtype=torch.long).reshape(2, -1)
+
+
+def radius_graph(x, r, batch=None, loop=False, max_num_neighbors=32, flow='source_to_target'):
+    row, col = radius(x, x, r, batch, batch, max_num_neighbors if loop else max_num_neighbors + 1)
+    row, col = (col, row) if flow == 'source_to_target' else (row, col)
+    if not loop:
+        mask = row != col
+        row, col = row[mask], col[mask]
+    return torch.stack([row, col], dim=0)

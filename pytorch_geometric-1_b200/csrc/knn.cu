@@ -4,8 +4,10 @@
 //
 // One thread per query point, 64 queries per CTA.  The candidates of the clouds the CTA
 // touches stream through shared memory in tiles of 64 points; every thread keeps the k best
-// (squared distance, index) pairs seen so far in a sorted list and inserts a candidate only
-// when it beats the current k-th.  Candidates are visited in ascending index and a candidate
+// (squared distance, index) pairs seen so far in a sorted list — in SHARED memory, laid out
+// [rank][thread] so that the dynamically indexed insertion is bank-conflict free (round 1
+// kept it in a per-thread array, i.e. a 512-byte local-memory stack frame) — and inserts a
+// candidate only when it beats the current k-th (kept in a register).  Candidates are visited in ascending index and a candidate
 // displaces only on a strictly smaller distance, so ties resolve to the lower index — the
 // order of a stable sort by (distance, index).  Distances are fp32, accumulated over the
 // coordinates in order with fused multiply-adds.
@@ -40,8 +42,8 @@ knn_kernel(const float* __restrict__ x, int64_t ldx, int D, const int64_t* __res
     sq[r * qs + d] = q0 + r < n ? x[(q0 + r) * ldx + d] : 0.f;
   }
   __syncthreads();
-  float bd[kKnnMaxK];
-  int bi[kKnnMaxK];
+  float* bd = sc + kKnnThreads * D + t;             // bd[r * 64]: rank r of this thread's list
+  int* bi = reinterpret_cast<int*>(sc + kKnnThreads * D + kKnnThreads * k) + t;
   int have = 0;
   float worst = 3.402823466e38f;                    // k-th best so far (register copy of bd[k-1])
   const float* myq = sq + t * qs;
@@ -78,19 +80,19 @@ knn_kernel(const float* __restrict__ x, int64_t ldx, int D, const int64_t* __res
       }
       if (have == k && !(dist < worst)) continue;
       int pos = have < k ? have : k - 1;            // insertion: shift the worse entries down
-      while (pos > 0 && dist < bd[pos - 1]) {
-        bd[pos] = bd[pos - 1];
-        bi[pos] = bi[pos - 1];
+      while (pos > 0 && dist < bd[(pos - 1) * kKnnThreads]) {
+        bd[pos * kKnnThreads] = bd[(pos - 1) * kKnnThreads];
+        bi[pos * kKnnThreads] = bi[(pos - 1) * kKnnThreads];
         --pos;
       }
-      bd[pos] = dist;
-      bi[pos] = (int)j;
+      bd[pos * kKnnThreads] = dist;
+      bi[pos * kKnnThreads] = (int)j;
       if (have < k) ++have;
-      if (have == k) worst = bd[k - 1];
+      if (have == k) worst = bd[(k - 1) * kKnnThreads];
     }
   }
   if (live) {
-    for (int r = 0; r < k; ++r) nbr[q * k + r] = r < have ? bi[r] : -1;
+    for (int r = 0; r < k; ++r) nbr[q * k + r] = r < have ? bi[r * kKnnThreads] : -1;
   }
 }
 
@@ -111,9 +113,12 @@ int pygb_knn_graph(const float* x, int64_t ldx, int64_t n, int D, const int64_t*
   }
   if (n == 0) return PYGB_OK;
   PYGB_REQUIRE(x && batch && ptr && nbr, "pygb_knn_graph: null pointer");
-  const size_t smem = (size_t)kKnnThreads * ((D | 1) + D) * sizeof(float);
+  const size_t smem = (size_t)kKnnThreads * ((D | 1) + D + 2 * k) * sizeof(float);
   const unsigned grid = (unsigned)ceil_div(n, kKnnThreads);
   if (D <= 4) {
+    if (smem > 48 * 1024)
+      PYGB_CUDA(cudaFuncSetAttribute(knn_kernel<true>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     knn_kernel<true><<<grid, kKnnThreads, smem, as_stream(s)>>>(x, ldx, D, batch, ptr, n, k, loop,
                                                                 nbr);
   } else {

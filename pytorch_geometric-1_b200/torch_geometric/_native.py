@@ -76,6 +76,8 @@ SIGNATURES = {
     'pygb_gemm_xw': (_I, [_P, _L, _L, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _I, _P, _Z, _P]),
     'pygb_gemm_xw_bf16': (_I, [_P, _L, _L, _L, _P, _L, _L, _P, _I, _P, _L, _P, _Z, _P]),
     'pygb_knn_graph': (_I, [_P, _L, _L, _I, _P, _P, _I, _I, _P, _P]),
+    'pygb_fps': (_I, [_P, _L, _L, _I, _P, _P, _P, _L, _P, _P, _P]),
+    'pygb_radius': (_I, [_P, _L, _P, _L, _I, _P, _P, _L, _F, _I, _I, _P, _P, _P]),
     'pygb_gemm_xtg_workspace': (_Z, [_L, _L, _L]),
     'pygb_gemm_xtg': (_I, [_P, _L, _P, _L, _L, _L, _L, _P, _L, _I, _P, _Z, _P]),
     'pygb_gat_edge_grad': (_I, [_P, _L, _P, _P, _I, _I, _F, _P, _P, _P, _L, _P, _L, _P, _P, _L,

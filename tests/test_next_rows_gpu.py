@@ -249,3 +249,87 @@ def test_dynamic_edge_conv_uses_knn_kernel(dev):
     names = [e[0] for e in nat.event_log]
     nat.event_log = None
     assert 'pygb_knn_graph' in names and out.shape == (512, 16)
+
+
+# ---- f4: fps / radius / radius_graph (examples/pointnet++.py:39-41,46-48) -----------------
+def _grid_cloud(n, seed):
+    """Coordinates on a 1/8 grid: every squared distance is exact in fp32 (and ties are
+    frequent), so the selection order can be compared index for index."""
+    g = torch.Generator().manual_seed(seed)
+    return ((torch.rand(n, 3, generator=g) * 2 - 1) * 8).round() / 8
+
+
+@pytest.mark.parametrize('ratio', [0.5, 0.25, 1.0])
+def test_fps_matches_loop_reference_including_ties(dev, ratio):
+    from torch_geometric.nn import fps
+    sizes = [130, 1, 77, 300]
+    x = _grid_cloud(sum(sizes), 3)
+    batch = torch.cat([torch.full((s,), b) for b, s in enumerate(sizes)]).long()
+    got = fps(x.to(dev), batch.to(dev), ratio=ratio, random_start=False)
+    ref = R.fps(x, batch, ratio)
+    assert got.dtype == torch.long and torch.equal(got.cpu(), ref)
+    assert torch.equal(got, fps(x.to(dev), batch.to(dev), ratio=ratio, random_start=False))
+    # random start: a valid farthest-point sequence from whatever start was drawn
+    rnd = fps(x.to(dev), batch.to(dev), ratio=ratio, random_start=True).cpu()
+    assert rnd.numel() == ref.numel()
+    assert torch.equal(batch[rnd], batch[ref])
+    starts, o = [], 0
+    for s in sizes:
+        m = -(-int(round(ratio * s * 1e6)) // 10 ** 6)
+        starts.append(int(rnd[o]) - int((batch < len(starts)).sum()))
+        o += m
+    assert torch.equal(rnd, R.fps(x, batch, ratio, start=starts))
+    assert fps(torch.zeros(0, 3, device=dev)).numel() == 0
+
+
+def test_fps_on_cfg4_sized_clouds(dev):
+    """32 x 1,024 points, ratio 0.5 (examples/pointnet++.py:39): the samples are distinct, per
+    cloud, and each one maximises the distance to the earlier ones (checked in fp64)."""
+    from torch_geometric.nn import fps
+    g = torch.Generator().manual_seed(1)
+    x = torch.rand(32 * 1024, 3, generator=g) * 2 - 1
+    batch = torch.arange(32).repeat_interleave(1024)
+    idx = fps(x.to(dev), batch.to(dev), ratio=0.5, random_start=False).cpu()
+    assert idx.numel() == 32 * 512 and idx.unique().numel() == idx.numel()
+    assert torch.equal(batch[idx], torch.arange(32).repeat_interleave(512))
+    xd = x.double()
+    for c in (0, 17, 31):
+        sel = idx[c * 512:(c + 1) * 512]
+        pts = xd[c * 1024:(c + 1) * 1024]
+        assert int(sel[0]) == c * 1024
+        dmin = torch.full((1024,), float('inf'), dtype=torch.float64)
+        for t in range(40):
+            dmin = torch.minimum(dmin, ((pts - xd[sel[t]]) ** 2).sum(1))
+            nxt = int(sel[t + 1]) - c * 1024
+            assert dmin[nxt] >= dmin.max() * (1 - 1e-6)
+
+
+@pytest.mark.parametrize('max_nn', [4, 32])
+def test_radius_and_radius_graph_match_loop_reference(dev, max_nn):
+    from torch_geometric.nn import radius, radius_graph
+    sizes = [90, 40, 1, 120]
+    x = _grid_cloud(sum(sizes), 5)
+    bx = torch.cat([torch.full((s,), b) for b, s in enumerate(sizes)]).long()
+    sel = torch.arange(0, x.size(0), 3)
+    y, by = x[sel] + 0.125, bx[sel]
+    got = radius(x.to(dev), y.to(dev), 0.5, bx.to(dev), by.to(dev), max_num_neighbors=max_nn)
+    ref = R.radius(x, y, 0.5, bx, by, max_nn)
+    assert torch.equal(got.cpu(), ref)
+    for loop in (False, True):
+        for flow in ('source_to_target', 'target_to_source'):
+            gg = radius_graph(x.to(dev), 0.5, bx.to(dev), loop=loop, max_num_neighbors=max_nn,
+                              flow=flow)
+            rr = R.radius_graph(x, 0.5, bx, loop=loop, max_num_neighbors=max_nn, flow=flow)
+            assert torch.equal(gg.cpu(), rr), (loop, flow)
+    assert radius(x.to(dev), torch.zeros(0, 3, device=dev), 0.5).shape == (2, 0)
+
+
+def test_knn_graph_kernel_large_k_and_ties(dev):
+    """k-best list in shared memory (round 2): k up to 64, tie rule = lower index."""
+    from torch_geometric.nn import knn_graph
+    x = _grid_cloud(400, 9)
+    batch = torch.cat([torch.zeros(150), torch.ones(250)]).long()
+    for k in (1, 20, 64):
+        got = knn_graph(x.to(dev), k, batch.to(dev)).cpu()
+        ref = R.knn_graph(x, k, batch)
+        assert torch.equal(got, ref), k
