@@ -58,6 +58,9 @@ CONFIG_WORKLOADS = ('pubmed_pruning', 'reddit_gat', 'edgeconv_knn')
 METRIC = 'propagate_edges_per_sec'
 UNIT = 'edges/s'
 L2_BYTES = 126 * 2 ** 20
+# row chunks of the pipelined layer-1 aggregation -> routed transform (dist/sliced.py), per
+# world size: measured where it pays (profiles/r02_multi_gpu.md), off elsewhere
+DEFAULT_CHUNKS = {8: 4}
 
 
 def parse():
@@ -82,6 +85,9 @@ def parse():
     ap.add_argument('--chunks', type=int, default=-1,
                     help='sliced layout: row chunks of the layer-1 aggregation pipelined against '
                          'the routed transform (-1 = library default)')
+    ap.add_argument('--gemm-ctas', type=int, default=0,
+                    help='sliced layout, chunked pipeline: SMs of the overlapped routed transform '
+                         '(0 = derived from the sizes)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-halo-rows', action='store_true',
@@ -511,8 +517,9 @@ def run_b200(args):
             graph = SlicedGraph(ei_full, norm_full, n, rank, world,
                                 transport='peer' if peer else 'collective', row_groups=row_groups,
                                 fence_mode=args.fence)
-            if args.chunks >= 0 and hasattr(graph, 'set_chunks'):
-                graph.set_chunks(args.chunks)
+            if peer:
+                graph.transport.gemm_ctas = args.gemm_ctas
+                graph.set_chunks(args.chunks if args.chunks >= 0 else DEFAULT_CHUNKS.get(world, 1))
             x_in = graph.slice_cols(x_dev)                  # this rank's columns of all rows
             x_rows = graph.local_rows(x_dev).contiguous()   # e2e: every rank uploads its rows only
             n_rows_local = n

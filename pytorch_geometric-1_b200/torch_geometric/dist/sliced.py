@@ -236,7 +236,7 @@ class PeerTransport(object):
         self._tabs = {}
         self._flag = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._side = None               # high-priority stream of the chunked pipeline
-        self.gemm_ctas = 32             # SMs given to the routed transform while it overlaps
+        self.gemm_ctas = 0              # SMs of the overlapped routed transform (0 = from the sizes)
         nat.load()
 
     # ---- arena ---------------------------------------------------------------------
@@ -432,6 +432,13 @@ class PeerTransport(object):
         if sliced:
             rows_all = rows_all.view(p.Gc, p.blk, Fca)
         rot = ((p.cg + 1) % p.Gc) * blk_c if self.rotate else 0
+        # SMs for the overlapped transform: enough that its tensor work (3xTF32, ~4.5 TFLOP/s
+        # per SM) keeps pace with what NVLink takes (~700 GB/s of the epilogue's peer stores)
+        gemm_ctas = self.gemm_ctas
+        if gemm_ctas <= 0:
+            flops = 6.0 * p.n_local * w.size(0) * w.size(1)
+            t_link = max((p.world_size - 1) * p.n_local * Fco * 4 / 700e9, 1e-6)
+            gemm_ctas = int(min(max(flops / (4.5e12 * t_link) + 1, 24), 96))
         for c in range(C):
             adj_c, w_c = graph.chunk(c)
             if sliced:
@@ -442,7 +449,7 @@ class PeerTransport(object):
                               [self._peer[p.rg * p.Gc + j] + base for j in range(p.Gc)])
             ops.seg_gather_reduce_routed_raw(cols[:, :Fca], adj_c.dst, w_c, None, tab, blk_c, ldo,
                                              start_row=rot,
-                                             max_ctas=-self.gemm_ctas if c > 0 else 0)
+                                             max_ctas=-gemm_ctas if c > 0 else 0)
             self.fence()
             ev = torch.cuda.Event()
             ev.record(main)
@@ -454,7 +461,7 @@ class PeerTransport(object):
                         rows_all[c * blk_c:c * blk_c + n_c]
                     ops.gemm_xw_routed_raw(a, w, bias, Fco, cols_tab, p.lo + c * blk_c, Fco, relu,
                                            p.Gr, rows=n_c,
-                                           max_ctas=self.gemm_ctas if c + 1 < C else 0)
+                                           max_ctas=gemm_ctas if c + 1 < C else 0)
         main.wait_stream(side)
         self.bytes_sent_total += (p.Gc - 1) * p.blk * Fca * 4
         self._sent_cols(Fco)

@@ -82,10 +82,13 @@ class CSR(object):
         return self.rowptr.device
 
 
-def build_csr(key, other, n_rows, n_cols=None):
+def build_csr(key, other, n_rows, n_cols=None, validated=False):
     """Sort ``key`` (int64 [E]) into a CSR with ``n_rows`` rows; ``other`` (int64
     [E], optional) becomes ``col``.  Raises ``IndexError`` for out-of-range
-    indices (one device->host read of a status word per build)."""
+    indices (one device->host read of a status word per build) — unless the caller
+    vouches that the ids were range-checked already (``validated``: an ``edge_index'``
+    that came out of the self-loop pass, which checks every id behind the read it
+    needs anyway), so the GCN first call pays one host synchronisation, not three."""
     dev = nat.require_cuda(key, other)
     if key.dtype != torch.long or (other is not None and other.dtype != torch.long):
         raise TypeError('index tensors must be int64')
@@ -103,7 +106,7 @@ def build_csr(key, other, n_rows, n_cols=None):
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     nat.call('pygb_csr_build', dev, nat.ptr(key), nat.ptr(other), E, n_rows, n_cols,
              nat.ptr(rowptr), nat.ptr(perm), nat.ptr(col), nat.ptr(status), nat.ptr(ws), ws_bytes)
-    st = int(status.item())
+    st = 0 if validated else int(status.item())
     if st == 1:
         raise IndexError('index out of range: expected values in [0, {})'.format(n_rows))
     if st == 2:
@@ -176,8 +179,12 @@ class Adj(object):
         self.i, self.j = i, 1 - i
         self.size = (int(size[0]), int(size[1]))
         self.E = edge_index.size(1)
+        # ids already range-checked against this node count by utils.loop._apply?
+        vn = getattr(edge_index, '_pygb_valid_n', None)
+        self._validated = vn is not None and vn <= min(self.size) and \
+            getattr(edge_index, '_pygb_valid_version', -1) == edge_index._version
         self.dst = build_csr(edge_index[self.i], edge_index[self.j], self.size[self.i],
-                             self.size[self.j])
+                             self.size[self.j], self._validated)
         self._src = None
         self._wcache = {}
         self._idx = {}
@@ -194,7 +201,9 @@ class Adj(object):
     def src(self):
         if self._src is None:
             ei = self.edge_index
-            self._src = build_csr(ei[self.j], ei[self.i], self.size[self.j], self.size[self.i])
+            # the dst build (or the self-loop pass) has range-checked both rows
+            self._src = build_csr(ei[self.j], ei[self.i], self.size[self.j], self.size[self.i],
+                                  True)
         return self._src
 
     @property

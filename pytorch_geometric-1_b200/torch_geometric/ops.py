@@ -17,6 +17,7 @@ NEG_INF = float('-inf')
 # padded, else the one-warp-per-row kernel.  STREAM_T forces the item size (tests).
 STREAM = True
 STREAM_T = None
+LINE_ALIGN = os.environ.get('PYGB_LINE_ALIGN', '1') not in ('', '0')
 
 
 def _rows2d(x):
@@ -59,6 +60,43 @@ def _f32(t):
 # --------------------------------------------------------------------------
 # raw (no autograd) launches
 # --------------------------------------------------------------------------
+_seen_wide = collections.OrderedDict()     # identities of large gather sources seen once
+_line_cache = collections.OrderedDict()    # identity -> copy with a 128-byte multiple row stride
+
+
+def _line_aligned_rows(x2):
+    """A large, constant gather source whose rows are not whole 128-byte lines (cfg5 layer 1:
+    F = 100 fp32 = 400-byte rows that start mid-sector, 0.89 of the HBM peak against 1.1 at
+    F = 256 — profiles/r01_k1_shapes.md) is gathered from a copy with the row stride padded to
+    128 bytes.  Like the sorted graph the copy is made once per tensor identity — and only for
+    a tensor that is seen a second time unchanged, so a source that is rewritten every step
+    (end-to-end uploads) is never copied."""
+    esz = x2.element_size()
+    row_b = x2.size(1) * esz
+    if (row_b % 128 == 0 or row_b < 256 or x2.numel() * esz < (64 << 20) or x2.requires_grad
+            or x2.stride(1) != 1 or (x2.stride(0) * esz) % 128 == 0):
+        return x2
+    key = (x2.data_ptr(), tuple(x2.shape), tuple(x2.stride()), x2._version, x2.device.index,
+           x2.dtype)
+    hit = _line_cache.get(key)
+    if hit is not None:
+        _line_cache.move_to_end(key)
+        return hit[0]
+    if key not in _seen_wide:
+        _seen_wide[key] = True
+        while len(_seen_wide) > 16:
+            _seen_wide.popitem(last=False)
+        return x2
+    ld = (row_b + 127) // 128 * 128 // esz
+    xp = torch.empty((x2.size(0), ld), dtype=x2.dtype, device=x2.device)
+    xp[:, :x2.size(1)].copy_(x2)
+    xp[:, x2.size(1):].zero_()
+    out = xp[:, :x2.size(1)]
+    _line_cache[key] = (out, x2)
+    while len(_line_cache) > 2:
+        _line_cache.popitem(last=False)
+    return out
+
 def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=None,
                           heads=None, idx_key=None):
     """out[i] = reduce_p w_p * x[idx[p]] over the rows of ``csr``.  ``idx`` is ``csr.col``,
@@ -66,6 +104,8 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
     dev = nat.require_cuda(x, idx, w, bias)
     x2 = _rows2d(x)
     F = x2.size(1)
+    if heads is None and wperm is None and STREAM and LINE_ALIGN:
+        x2 = _line_aligned_rows(x2)
     # rows padded to a 16-byte multiple keep the kernel on its 128-bit path
     vec = 16 // x2.element_size()
     ldo = (F + vec - 1) // vec * vec if F > 1 else F

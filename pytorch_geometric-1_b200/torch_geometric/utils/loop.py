@@ -50,6 +50,10 @@ def _apply(edge_index, N, mode, edge_weight, fill_value):
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
     nat.call('pygb_apply_loops', dev, nat.ptr(edge_index), E, N, mode, n_loops, nat.ptr(w),
              float(fill_value), nat.ptr(out), nat.ptr(w_out), nat.ptr(ws), ws_bytes)
+    if mode != nat.LOOPS_ADD and mode != nat.LOOPS_REMOVE and E > 0:
+        # every id was range-checked by the scan above: the CSR build can skip its own check
+        out._pygb_valid_n = int(N)
+        out._pygb_valid_version = out._version
     return out, w_out, n_loops
 
 

@@ -125,20 +125,30 @@ def test_cfg4_with_noise_edges_bit_exact(dev):
     assert torch.equal(gv.cpu(), rv) and torch.equal(garg.cpu(), rarg)
 
 
-@pytest.mark.parametrize('scale,backward', [(16, False), (64, True)])
-def test_cfg3_gat_reddit_shape_scaled_vs_oracle(dev, scale, backward):
+@pytest.mark.parametrize('scale,backward,slope', [(16, False, 0.2), (64, True, 1.0), (64, True, 0.2)])
+def test_cfg3_gat_reddit_shape_scaled_vs_oracle(dev, scale, backward, slope):
     """Reddit-shaped log-normal graph at 1/scale (same mean in-degree ~492), x [N, 602],
     GATConv(602, 8, heads=8): K = 602 exercises the unaligned-row tcgen05 path, H = 8 / C = 8
     the streaming fused kernels.  1/16 forward (7.2 M edges through the CPU oracle), 1/64 with
-    the backward."""
+    the backward (and 1 % self-loops + 1 % duplicate edges).
+
+    Backward at ``negative_slope=0.2``: leaky-relu has a kink at 0, and with 29 M (edge, head)
+    logits a handful lie within the forward rounding error of it, so their derivative (1 vs 0.2)
+    differs between ANY two fp32 implementations; an edge with a large attention weight then
+    moves one row of d xw by ~1e-3 of the maximum (measured: 5 outlier rows, both backward
+    kernel generations agree with each other to 1e-7 and differ from the oracle in the same
+    rows — tools/debug_r2b.py).  So the strict element-wise comparison runs with slope 1.0 (no
+    kink, everything else identical) and the slope-0.2 run must agree in all but 1e-4 of the
+    elements."""
     from torch_geometric.datasets import synthetic
     from torch_geometric.nn import GATConv
+    from util import elem_err
     n, pairs = 232965 // scale, 57307946 // scale
     data = synthetic.reddit_like(seed=2, num_nodes=n, num_pairs=pairs)
     ei = synthetic.add_noise_edges(data.edge_index, n, 0.01, 0.01, 3) if backward else data.edge_index
     torch.manual_seed(2)
-    conv = GATConv(602, 8, heads=8).to(dev)
-    ref = O.GATConv(602, 8, heads=8)
+    conv = GATConv(602, 8, heads=8, negative_slope=slope).to(dev)
+    ref = O.GATConv(602, 8, heads=8, negative_slope=slope)
     with torch.no_grad():
         conv.bias.uniform_(-0.5, 0.5)
     _sync(conv, ref)
@@ -149,15 +159,28 @@ def test_cfg3_gat_reddit_shape_scaled_vs_oracle(dev, scale, backward):
     else:
         with torch.no_grad():
             ra, rb = ref(a, ei), conv(b, ei.to(dev))
-    assert_close(rb, ra, 2e-5, 'cfg3 forward 1/{}'.format(scale))
-    if backward:
-        g = torch.randn(ra.shape, generator=torch.Generator().manual_seed(3))
-        ra.backward(g)
-        rb.backward(g.to(dev))
-        assert_close(b.grad, a.grad, 2e-4, 'cfg3 dx')
-        assert_close(conv.weight.grad, ref.weight.grad, 2e-4, 'cfg3 dW')
-        assert_close(conv.att.grad, ref.att.grad, 2e-4, 'cfg3 datt')
+    # X.W at K = 602 (3xTF32, split accumulator) feeds an exponential: 2e-5 relative with a
+    # floor of 5e-6 of the largest entry
+    assert_close(rb, ra, 2e-5, 'cfg3 forward 1/{}'.format(scale), floor=5e-6)
+    if not backward:
+        return
+    g = torch.randn(ra.shape, generator=torch.Generator().manual_seed(3))
+    ra.backward(g)
+    rb.backward(g.to(dev))
+    pairs_ = [(b.grad, a.grad, 'dx'), (conv.weight.grad, ref.weight.grad, 'dW'),
+              (conv.att.grad, ref.att.grad, 'datt'), (conv.bias.grad, ref.bias.grad, 'dbias')]
+    if slope == 1.0:
+        for got, want, what in pairs_:
+            assert_close(got, want, 2e-4, 'cfg3 ' + what)
+    else:
         assert_close(conv.bias.grad, ref.bias.grad, 2e-4, 'cfg3 dbias')
+        got, want = b.grad.detach().cpu().double(), a.grad.double()
+        bound = 2e-4 * want.abs() + 2e-5 * want.abs().max()
+        frac_bad = float(((got - want).abs() > bound).double().mean())
+        assert frac_bad <= 1e-4, 'cfg3 dx: {:.2e} of the elements outside the bound'.format(frac_bad)
+        # the parameter gradients are sums over all rows: the few kink rows move them by ~1e-3
+        for got, want, what in pairs_[1:3]:
+            assert_close(got, want, 2e-3, 'cfg3 ' + what + ' (kink-limited)', floor=2e-3)
 
 
 def test_cfg3_gat_full_size_sampled_rows_fp64(dev):

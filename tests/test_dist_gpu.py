@@ -23,6 +23,29 @@ def _free_port():
     return p
 
 
+def _join_all(procs, q=None, limit=150):
+    """Join with one shared deadline; a rank that hangs (e.g. in a collective its peer never
+    reached because it failed) is killed instead of being left on the GPU."""
+    import time
+    deadline = time.time() + limit
+    for p in procs:
+        p.join(max(deadline - time.time(), 1))
+    hung = [p for p in procs if p.exitcode is None]
+    for p in hung:
+        p.kill()
+        p.join(10)
+    codes = [p.exitcode for p in procs]
+    if hung or any(c != 0 for c in codes):
+        msgs = []
+        if q is not None:
+            try:
+                while True:
+                    msgs.append(q.get_nowait())
+            except Exception:
+                pass
+        raise AssertionError('rank exit codes {} ({} hung): {}'.format(codes, len(hung), msgs))
+
+
 def _worker(rank, world, port, q):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -80,9 +103,7 @@ def test_dist_gcn_two_gpus_nccl():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    for p in procs:
-        p.join(300)
-        assert p.exitcode == 0
+    _join_all(procs, q)
     status, err = q.get(timeout=10)
     assert status == 'ok', err
     assert err <= 2e-5, err
@@ -131,7 +152,13 @@ def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence=
                 names = [e[0] for e in nat.event_log]
                 nat.event_log = None
             torch.cuda.synchronize()
-            assert torch.equal(out_local, plain), 'chunked pipeline changed the result'
+            # same addends per row in the same order; a row cut by a work-item boundary is
+            # combined from pieces, and the cut points move with the chunk's slot numbering,
+            # so the last bits may differ (fp32 association) — compared at 1e-6 of the maximum
+            rel = float((out_local - plain).abs().max() / plain.abs().max())
+            ok = torch.tensor([1.0 if rel <= 1e-6 else 0.0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)       # fail on every rank together
+            assert float(ok) == 1.0, 'chunked pipeline changed the result: {:.3e}'.format(rel)
             assert names.count('pygb_gemm_xw_routed') == chunks + 1, names
         parts = [torch.zeros(pl.blk, 47, device=dev) for _ in range(world)]
         pad = torch.zeros(pl.blk, 47, device=dev)
@@ -164,9 +191,7 @@ def _run_sliced(world, transport, x_layout, row_groups=1, fence='flags', chunks=
              for r in range(world)]
     for p in procs:
         p.start()
-    for p in procs:
-        p.join(300)
-        assert p.exitcode == 0
+    _join_all(procs, q)
     status, err = q.get(timeout=10)
     assert status == 'ok', err
     assert err <= 2e-5, err
