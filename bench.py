@@ -88,6 +88,9 @@ def parse():
     ap.add_argument('--gemm-ctas', type=int, default=0,
                     help='sliced layout, chunked pipeline: SMs of the overlapped routed transform '
                          '(0 = derived from the sizes)')
+    ap.add_argument('--sweep-chunks', default='',
+                    help='sliced layout: also time these "chunks:gemm_ctas" settings (comma list, '
+                         'e.g. 1:0,2:0,4:0,4:48) for 10 steps each and report them under chunk_sweep')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-halo-rows', action='store_true',
@@ -604,6 +607,35 @@ def run_b200(args):
         out = forward(x_in)
     barrier()
 
+    # ---- optional: sweep of the pipeline settings (tuning aid, outside the timed region) ----
+    chunk_sweep = None
+    if world > 1 and args.sweep_chunks and args.dist == 'sliced' and dtype == torch.float32:
+        chunk_sweep = []
+        keep = (graph.chunks, graph.transport.gemm_ctas)
+        for item in args.sweep_chunks.split(','):
+            c_, g_ = (int(v) for v in item.split(':'))
+            graph.transport.gemm_ctas = g_
+            graph.set_chunks(c_)
+            for _ in range(3):
+                o_ = forward(x_in)
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            for _ in range(10):
+                o_ = forward(x_in)
+            s1.record()
+            barrier()
+            t = torch.tensor([s0.elapsed_time(s1) / 10], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            rel = float((o_ - out).abs().max() / out.abs().max())
+            chunk_sweep.append({'chunks': c_, 'gemm_ctas': g_, 'ms_per_step': float(t),
+                                'max_rel_diff_vs_default': rel})
+        graph.transport.gemm_ctas = keep[1]
+        graph.set_chunks(keep[0])
+        for _ in range(2):
+            out = forward(x_in)
+        barrier()
+
     # ---- N>1: the distributed result against the rank's single-GPU rows --------
     if world > 1 and not args.no_verify:
         tol = 1e-5 if dtype == torch.float32 else 2e-2
@@ -779,7 +811,7 @@ def run_b200(args):
             'max_rel_err': None if verify is None else verify['max_rel_err'],
             'verify': verify,
             'roofline': roofline, 'breakdown_ms_per_step': breakdown, 'halo': halo,
-            'halo_rows': halo_rows, 'cpu_baseline': cpu, 'e2e': e2e,
+            'halo_rows': halo_rows, 'chunk_sweep': chunk_sweep, 'cpu_baseline': cpu, 'e2e': e2e,
             'gpu_launches': launches, 'host_issue_ms_per_step': host_ms,
             'clocks': clocks,
         }

@@ -21,10 +21,10 @@ def fps(x, batch=None, ratio=0.5, random_start=True):
     """Indices of ``ceil(ratio * n_b)`` farthest-point samples of every example, in selection
     order.  ``random_start=False`` starts at each example's first point (deterministic)."""
     n = x.size(0)
-    x = x.view(n, -1)
     dev = nat.require_cuda(x, batch)
     if n == 0:
         return torch.empty(0, dtype=torch.long, device=dev)
+    x = x.view(n, -1)
     x = x.float()
     x = x if x.stride(-1) == 1 else x.contiguous()
     if batch is None:
@@ -51,13 +51,13 @@ def radius(x, y, r, batch_x=None, batch_y=None, max_num_neighbors=32, _skip_same
     the same example within distance ``r``: ``[2, E]`` with row 0 = index into y, row 1 = index
     into x."""
     dev = nat.require_cuda(x, y, batch_x, batch_y)
-    x, y = x.view(x.size(0), -1).float(), y.view(y.size(0), -1).float()
-    x = x if x.stride(-1) == 1 else x.contiguous()
-    y = y if y.stride(-1) == 1 else y.contiguous()
-    assert x.size(1) == y.size(1)
     ny = y.size(0)
     if ny == 0 or x.size(0) == 0:
         return torch.empty((2, 0), dtype=torch.long, device=dev)
+    x, y = x.view(x.size(0), -1).float(), y.view(ny, -1).float()
+    x = x if x.stride(-1) == 1 else x.contiguous()
+    y = y if y.stride(-1) == 1 else y.contiguous()
+    assert x.size(1) == y.size(1)
     if batch_x is None:
         batch_x = torch.zeros(x.size(0), dtype=torch.long, device=dev)
     if batch_y is None:

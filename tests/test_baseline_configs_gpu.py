@@ -138,8 +138,8 @@ def test_cfg3_gat_reddit_shape_scaled_vs_oracle(dev, scale, backward, slope):
     moves one row of d xw by ~1e-3 of the maximum (measured: 5 outlier rows, both backward
     kernel generations agree with each other to 1e-7 and differ from the oracle in the same
     rows — tools/debug_r2b.py).  So the strict element-wise comparison runs with slope 1.0 (no
-    kink, everything else identical) and the slope-0.2 run must agree in all but 1e-4 of the
-    elements."""
+    kink, everything else identical) and the slope-0.2 run must agree in all but 0.5 % of the
+    rows of d x."""
     from torch_geometric.datasets import synthetic
     from torch_geometric.nn import GATConv
     from util import elem_err
@@ -176,8 +176,9 @@ def test_cfg3_gat_reddit_shape_scaled_vs_oracle(dev, scale, backward, slope):
         assert_close(conv.bias.grad, ref.bias.grad, 2e-4, 'cfg3 dbias')
         got, want = b.grad.detach().cpu().double(), a.grad.double()
         bound = 2e-4 * want.abs() + 2e-5 * want.abs().max()
-        frac_bad = float(((got - want).abs() > bound).double().mean())
-        assert frac_bad <= 1e-4, 'cfg3 dx: {:.2e} of the elements outside the bound'.format(frac_bad)
+        bad_rows = int(((got - want).abs() > bound).any(dim=1).sum())
+        # measured: 5 of 3,640 rows (each one a node with an incident kink edge)
+        assert bad_rows <= max(n // 200, 1), 'cfg3 dx: {} of {} rows outside the bound'.format(bad_rows, n)
         # the parameter gradients are sums over all rows: the few kink rows move them by ~1e-3
         for got, want, what in pairs_[1:3]:
             assert_close(got, want, 2e-3, 'cfg3 ' + what + ' (kink-limited)', floor=2e-3)
