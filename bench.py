@@ -59,8 +59,10 @@ METRIC = 'propagate_edges_per_sec'
 UNIT = 'edges/s'
 L2_BYTES = 126 * 2 ** 20
 # row chunks of the pipelined layer-1 aggregation -> routed transform (dist/sliced.py), per
-# world size: measured where it pays (profiles/r02_multi_gpu.md), off elsewhere
-DEFAULT_CHUNKS = {8: 4}
+# world size: the r02 sweep on 8 and 4 GPUs found no setting that beats 1 (the narrow-slice
+# aggregation is issue-bound, so the SMs it cedes cost what the overlap gains —
+# profiles/r02_multi_gpu.md); kept as an option
+DEFAULT_CHUNKS = {}
 
 
 def parse():
@@ -88,6 +90,10 @@ def parse():
     ap.add_argument('--gemm-ctas', type=int, default=0,
                     help='sliced layout, chunked pipeline: SMs of the overlapped routed transform '
                          '(0 = derived from the sizes)')
+    ap.add_argument('--first-layer', default='own-rows', choices=['own-rows', 'cols'],
+                    help='sliced layout: the first aggregation over the rank\'s own row block at '
+                         'full width from the replicated input (default), or column-sliced like '
+                         'the other layers')
     ap.add_argument('--sweep-chunks', default='',
                     help='sliced layout: also time these "chunks:gemm_ctas" settings (comma list, '
                          'e.g. 1:0,2:0,4:0,4:48) for 10 steps each and report them under chunk_sweep')
@@ -523,14 +529,18 @@ def run_b200(args):
             if peer:
                 graph.transport.gemm_ctas = args.gemm_ctas
                 graph.set_chunks(args.chunks if args.chunks >= 0 else DEFAULT_CHUNKS.get(world, 1))
-            x_in = graph.slice_cols(x_dev)                  # this rank's columns of all rows
             x_rows = graph.local_rows(x_dev).contiguous()   # e2e: every rank uploads its rows only
             n_rows_local = n
             lo, hi = graph.plan.lo, graph.plan.hi
+            # the input features are static: they stay replicated (1 GB), and the first
+            # aggregation runs over the rank's own rows at full width — nothing to exchange
+            full_in = args.first_layer == 'own-rows' and peer
+            x_in = x_dev.clone() if full_in else graph.slice_cols(x_dev)
+            first_layout = 'full' if full_in else 'cols'
 
             def forward(x):
                 with torch.no_grad():
-                    h = sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols')
+                    h = sliced_gcn_forward(graph, x, layers, relu=True, x_layout=first_layout)
                     return F.log_softmax(h.float(), dim=1)
 
             def forward_rows(x):

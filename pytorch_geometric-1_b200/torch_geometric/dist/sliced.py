@@ -517,6 +517,23 @@ class SlicedGraph(object):
         self.chunks = 1
         self._chunk_graphs = {}
         self.device = edge_index.device
+        # in-edges of this rank's OWN row block (destinations renumbered from 0): the first
+        # layer of a forward whose input is replicated (`x_layout='full'`) aggregates them at
+        # full width with no exchange at all
+        self.own_adj = self.own_w = None
+        if build_adj:
+            from ..graph import Adj
+            t = edge_index[i]
+            m_own = (t >= p.lo) & (t < p.hi)
+            ei_o = edge_index[:, m_own].clone()
+            ei_o[i] -= p.lo
+            size = [0, 0]
+            size[i], size[1 - i] = p.n_local, num_nodes
+            self.own_adj = Adj(ei_o, i, size)
+            self.own_w = None if norm is None else \
+                self.own_adj.permuted(norm[m_own].float().contiguous(), 'dst')
+            self.num_edges_own = int(ei_o.size(1))
+            del t, m_own
         if p.Gr > 1:                                   # in-edges of the row group, renumbered
             t = edge_index[i]
             mask = (t >= p.g_lo) & (t < p.g_hi)
@@ -643,8 +660,11 @@ def sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols', aggregate=_
                        transform=_native_transform):
     """GCN forward with ``layers = [(weight [in,out], bias|None), ...]``; ReLU between
     layers when ``relu``.  ``x``: this rank's column slice ``[n_padded, Fc]``
-    (``x_layout='cols'``, see ``SlicedGraph.slice_cols``) or its rows ``[n_local, in]``
-    (``'rows'``).  Returns this rank's rows ``[n_local, out]`` of the last layer.
+    (``x_layout='cols'``, see ``SlicedGraph.slice_cols``), its rows ``[n_local, in]``
+    (``'rows'``), or the whole ``[N, in]`` matrix replicated on every rank (``'full'``: a static
+    input such as the dataset features — the first aggregation then runs over the rank's own
+    row block at full width, with nothing to exchange before or after it).  Returns this
+    rank's rows ``[n_local, out]`` of the last layer.
 
     Every layer aggregates at ``min(in, out)`` channels (``A (X W) = (A X) W``).  The
     forward is a chain of two primitives — aggregate (column layout -> row layout) and
@@ -664,6 +684,21 @@ def sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols', aggregate=_
     tr.prepare(max([p.widths(f, esz)[0] for w, _ in layers for f in w.shape] or [0]))
     state, kind = x, x_layout
     skip = False
+    if x_layout == 'full':
+        first = ops_seq[0] if ops_seq else None
+        if (first is not None and first[0] == 'agg' and aggregate is _native_aggregate
+                and graph.own_adj is not None and p.n_local > 0):
+            from .. import ops
+            _, F0, b0, act0 = first
+            csr = graph.own_adj.dst
+            state = ops.seg_gather_reduce_raw(x[:, :F0], csr, csr.col, 'sum', graph.own_w, None, b0)
+            if act0:
+                state = torch.relu_(state)
+            kind, skip = 'rows', True
+        elif first is not None and first[0] == 'agg':
+            state, kind = graph.slice_cols(x), 'cols'
+        else:
+            state, kind = x[p.lo:p.hi], 'rows'
     for n_op, op in enumerate(ops_seq):
         if skip:
             skip = False

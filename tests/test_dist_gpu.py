@@ -136,7 +136,12 @@ def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence=
         g = SlicedGraph(ei2, norm, n, rank, world, transport=transport, row_groups=row_groups,
                         fence_mode=fence)
         pl = g.plan
-        xin = g.slice_cols(x.to(dev)) if x_layout == 'cols' else g.local_rows(x.to(dev)).contiguous()
+        if x_layout == 'cols':
+            xin = g.slice_cols(x.to(dev))
+        elif x_layout == 'full':
+            xin = x.to(dev)                   # replicated static input: first layer over own rows
+        else:
+            xin = g.local_rows(x.to(dev)).contiguous()
         lay = [(w.to(dev), b.to(dev)) for w, b in layers]
         for _ in range(3):                    # buffer reuse across steps (double-buffered rows)
             out_local = sliced_gcn_forward(g, xin, lay, x_layout=x_layout)
@@ -198,7 +203,8 @@ def _run_sliced(world, transport, x_layout, row_groups=1, fence='flags', chunks=
 
 
 @pytest.mark.parametrize('transport,x_layout,row_groups', [
-    ('collective', 'cols', 1), ('peer', 'cols', 1), ('peer', 'rows', 1), ('peer', 'cols', 2)])
+    ('collective', 'cols', 1), ('peer', 'cols', 1), ('peer', 'rows', 1), ('peer', 'cols', 2),
+    ('peer', 'full', 1), ('peer', 'full', 2), ('collective', 'full', 1)])
 def test_sliced_gcn_two_gpus(transport, x_layout, row_groups):
     if torch.cuda.device_count() < 2:
         pytest.skip('needs two GPUs')
@@ -219,9 +225,10 @@ def test_sliced_gcn_four_gpus_two_row_groups(transport):
 
 
 @pytest.mark.parametrize('transport', ['collective', 'peer'])
-def test_sliced_gcn_one_gpu(transport):
+@pytest.mark.parametrize('x_layout', ['cols', 'full'])
+def test_sliced_gcn_one_gpu(transport, x_layout):
     """world_size 1: the same code path (routed stores into the rank's own arena)."""
-    _run_sliced(1, transport, 'cols')
+    _run_sliced(1, transport, x_layout)
 
 
 @pytest.mark.parametrize('chunks', [2, 8])
@@ -238,12 +245,13 @@ def test_sliced_gcn_two_gpus_chunked_pipeline(row_groups, chunks):
     _run_sliced(2, 'peer', 'cols', row_groups, fence='nccl', chunks=chunks)
 
 
-@pytest.mark.parametrize('chunks', [1, 4])
-def test_sliced_gcn_eight_gpus_two_by_four(chunks):
-    """The layout the driver's 8-GPU SCALE run uses: 2 row groups x 4 column slices, peer stores."""
+@pytest.mark.parametrize('x_layout,chunks', [('cols', 1), ('cols', 4), ('full', 1)])
+def test_sliced_gcn_eight_gpus_two_by_four(x_layout, chunks):
+    """The layout the driver's 8-GPU SCALE run uses: 2 row groups x 4 column slices, peer stores
+    ('full': the first aggregation over the rank's own rows from the replicated input)."""
     if torch.cuda.device_count() < 8:
         pytest.skip('needs eight GPUs')
-    _run_sliced(8, 'peer', 'cols', 2, fence='nccl', chunks=chunks)
+    _run_sliced(8, 'peer', x_layout, 2, fence='nccl', chunks=chunks)
 
 
 def test_routed_kernels_with_capped_grids(dev):
