@@ -90,10 +90,11 @@ def parse():
     ap.add_argument('--gemm-ctas', type=int, default=0,
                     help='sliced layout, chunked pipeline: SMs of the overlapped routed transform '
                          '(0 = derived from the sizes)')
-    ap.add_argument('--first-layer', default='own-rows', choices=['own-rows', 'cols'],
+    ap.add_argument('--first-layer', default='auto', choices=['auto', 'own-rows', 'cols'],
                     help='sliced layout: the first aggregation over the rank\'s own row block at '
-                         'full width from the replicated input (default), or column-sliced like '
-                         'the other layers')
+                         'full width from the replicated input, or column-sliced like the other '
+                         'layers; auto = own-rows when a column slice of the input would be narrower '
+                         'than 64 columns (4+ column slices: narrow slices are issue-bound)')
     ap.add_argument('--sweep-chunks', default='',
                     help='sliced layout: also time these "chunks:gemm_ctas" settings (comma list, '
                          'e.g. 1:0,2:0,4:0,4:48) for 10 steps each and report them under chunk_sweep')
@@ -534,7 +535,8 @@ def run_b200(args):
             lo, hi = graph.plan.lo, graph.plan.hi
             # the input features are static: they stay replicated (1 GB), and the first
             # aggregation runs over the rank's own rows at full width — nothing to exchange
-            full_in = args.first_layer == 'own-rows' and peer
+            full_in = peer and (args.first_layer == 'own-rows' or (
+                args.first_layer == 'auto' and graph.plan.widths(fin, itemsize)[1] < 64))
             x_in = x_dev.clone() if full_in else graph.slice_cols(x_dev)
             first_layout = 'full' if full_in else 'cols'
 
