@@ -468,6 +468,49 @@ class PeerTransport(object):
         self.fence()
         return self._view(self._c_off, p.n_padded, Fco)
 
+    def own_rows_transform_pipelined(self, graph, x, F0, w, bias, F_out, relu):
+        """First layer from a replicated input, pipelined: the aggregation of row chunk c+1 of
+        the rank's OWN rows (local output, no fence) runs while the routed transform of chunk c
+        sends its column blocks over NVLink from a second, high-priority stream with a capped
+        grid.  Unlike the column-sliced pipeline there is nothing to wait for between chunks —
+        the rows are local — and at full width the aggregation is HBM-bound, not issue-bound."""
+        from .. import ops
+        p = self.plan
+        C = graph.chunks
+        Fpo, Fco = p.widths(F_out, 4)
+        self.ensure(Fpo)
+        main = torch.cuda.current_stream(self.device)
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.device, priority=-1)
+        side = self._side
+        cols_tab = self._cols_table()
+        vec = 4
+        ld = (F0 + vec - 1) // vec * vec
+        rows = graph.buffer(('own_rows', F0), max(p.n_local, 1), ld, torch.float32)
+        gemm_ctas = self.gemm_ctas
+        if gemm_ctas <= 0:
+            flops = 6.0 * p.n_local * w.size(0) * w.size(1)
+            t_link = max((p.world_size - 1) * p.n_local * Fco * 4 / 700e9, 1e-6)
+            gemm_ctas = int(min(max(flops / (4.5e12 * t_link) + 1, 24), 96))
+        for c in range(C):
+            adj_c, w_c, r0, n_c = graph.own_chunk(c)
+            if n_c == 0:
+                continue
+            tab = self._table(('own', F0, c, C), [rows.data_ptr() + r0 * ld * 4])
+            ops.seg_gather_reduce_routed_raw(x[:, :F0], adj_c.dst, w_c, None, tab, max(n_c, 2), ld,
+                                             max_ctas=-gemm_ctas if c > 0 else 0)
+            ev = torch.cuda.Event()
+            ev.record(main)
+            with torch.cuda.stream(side):
+                side.wait_event(ev)
+                ops.gemm_xw_routed_raw(rows[r0:r0 + n_c, :F0], w, bias, Fco, cols_tab, p.lo + r0,
+                                       Fco, relu, p.Gr, rows=n_c,
+                                       max_ctas=gemm_ctas if c + 1 < C else 0)
+        main.wait_stream(side)
+        self._sent_cols(Fco)
+        self.fence()
+        return self._view(self._c_off, p.n_padded, Fco)
+
     def rows_to_cols(self, rows, F, relu=False):
         from .. import ops
         self._check(rows)
@@ -520,7 +563,7 @@ class SlicedGraph(object):
         # in-edges of this rank's OWN row block (destinations renumbered from 0): the first
         # layer of a forward whose input is replicated (`x_layout='full'`) aggregates them at
         # full width with no exchange at all
-        self.own_adj = self.own_w = None
+        self.own_adj = self.own_w = self.own_norm = None
         if build_adj:
             from ..graph import Adj
             t = edge_index[i]
@@ -530,8 +573,8 @@ class SlicedGraph(object):
             size = [0, 0]
             size[i], size[1 - i] = p.n_local, num_nodes
             self.own_adj = Adj(ei_o, i, size)
-            self.own_w = None if norm is None else \
-                self.own_adj.permuted(norm[m_own].float().contiguous(), 'dst')
+            self.own_norm = None if norm is None else norm[m_own].float().contiguous()
+            self.own_w = None if norm is None else self.own_adj.permuted(self.own_norm, 'dst')
             self.num_edges_own = int(ei_o.size(1))
             del t, m_own
         if p.Gr > 1:                                   # in-edges of the row group, renumbered
@@ -569,6 +612,8 @@ class SlicedGraph(object):
         self.chunks = chunks
         for c in range(chunks if chunks > 1 else 0):
             self.chunk(c)                           # sort the sub-graphs now, not in a timed step
+            if self.own_adj is not None:
+                self.own_chunk(c)
 
     def chunk(self, c):
         """(Adj, w_csr) of row chunk ``c``: the in-edges of rows ``[c*blk_c, (c+1)*blk_c)`` of
@@ -593,6 +638,38 @@ class SlicedGraph(object):
         adj.dst.flagged('col')
         self._chunk_graphs[c] = (adj, w)
         return adj, w
+
+    def own_chunk(self, c):
+        """(Adj, w_csr, first row, rows) of chunk ``c`` of the rank's own rows: the in-edges of
+        the contiguous row range, destinations renumbered from 0 (stable: same per-row order)."""
+        key = ('own', c, self.chunks)
+        hit = self._chunk_graphs.get(key)
+        if hit is not None:
+            return hit
+        from ..graph import Adj
+        p, i = self.plan, self.i
+        per = -(-p.n_local // self.chunks)
+        per = -(-per // 8) * 8
+        r0 = min(c * per, p.n_local)
+        n_c = min(per, p.n_local - r0)
+        if n_c <= 0:
+            hit = (None, None, r0, 0)
+        else:
+            ei_o = self.own_adj.edge_index
+            t = ei_o[i]
+            mask = (t >= r0) & (t < r0 + n_c)
+            ei = ei_o[:, mask].clone()
+            ei[i] -= r0
+            size = [0, 0]
+            size[i], size[1 - i] = max(n_c, 2), p.num_nodes
+            adj = Adj(ei, i, size)
+            w = None if self.own_norm is None else \
+                adj.permuted(self.own_norm[mask].contiguous(), 'dst')
+            adj.dst.items(None)
+            adj.dst.flagged('col')
+            hit = (adj, w, r0, n_c)
+        self._chunk_graphs[key] = hit
+        return hit
 
     def local_rows(self, x_global):
         return x_global[self.plan.lo:self.plan.hi]
@@ -690,18 +767,32 @@ def sliced_gcn_forward(graph, x, layers, relu=True, x_layout='cols', aggregate=_
                 and graph.own_adj is not None and p.n_local > 0):
             from .. import ops
             _, F0, b0, act0 = first
-            csr = graph.own_adj.dst
-            state = ops.seg_gather_reduce_raw(x[:, :F0], csr, csr.col, 'sum', graph.own_w, None, b0)
-            if act0:
-                state = torch.relu_(state)
-            kind, skip = 'rows', True
+            nxt_ = ops_seq[1] if len(ops_seq) > 1 else None
+            nxt2_ = ops_seq[2] if len(ops_seq) > 2 else None
+            if (getattr(graph, 'chunks', 1) > 1 and getattr(tr, 'fused', False) and b0 is None
+                    and not act0 and transform is _native_transform and F0 % 4 == 0
+                    and x.dtype == torch.float32 and nxt_ is not None and nxt_[0] == 'gemm'
+                    and nxt2_ is not None and nxt2_[0] == 'agg'):
+                _, k_, w_, b_, act_ = nxt_
+                fpo_, _ = p.widths(w_.size(1), esz)
+                wp_ = graph.padded(('w', k_), w_, F0, fpo_)
+                bp_ = graph.padded(('b', k_), b_, 0, fpo_)
+                state = tr.own_rows_transform_pipelined(graph, x, F0, wp_, bp_, w_.size(1), act_)
+                kind, skip = 'cols', 2
+            else:
+                csr = graph.own_adj.dst
+                state = ops.seg_gather_reduce_raw(x[:, :F0], csr, csr.col, 'sum', graph.own_w, None,
+                                                  b0)
+                if act0:
+                    state = torch.relu_(state)
+                kind, skip = 'rows', 1
         elif first is not None and first[0] == 'agg':
             state, kind = graph.slice_cols(x), 'cols'
         else:
             state, kind = x[p.lo:p.hi], 'rows'
     for n_op, op in enumerate(ops_seq):
         if skip:
-            skip = False
+            skip = int(skip) - 1
             continue
         nxt = ops_seq[n_op + 1] if n_op + 1 < len(ops_seq) else None
         nxt2 = ops_seq[n_op + 2] if n_op + 2 < len(ops_seq) else None

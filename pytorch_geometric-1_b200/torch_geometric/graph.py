@@ -143,6 +143,10 @@ class _LRU(object):
 
 
 def _ident(t):
+    """Cache key of an index tensor: storage pointer, shape, strides, autograd version counter,
+    device.  The version counter sees every in-place torch op, but NOT writes through ``.data``
+    or from foreign kernels: code that rewrites an ``edge_index`` buffer that way must call
+    ``torch_geometric.graph.clear_caches()``."""
     return (t.data_ptr(), tuple(t.shape), tuple(t.stride()), t._version, t.device.index)
 
 

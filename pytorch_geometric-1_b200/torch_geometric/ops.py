@@ -175,6 +175,8 @@ def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, re
     caller owns the destinations and orders the stores against their consumers."""
     dev = nat.require_cuda(x, w_csr, bias, out_tab)
     x2 = _rows2d(x)
+    if LINE_ALIGN:
+        x2 = _line_aligned_rows(x2)
     F = x2.size(1)
     vec = 16 // x2.element_size()
     if not (F > 1 and F % vec == 0 and x2.data_ptr() % 16 == 0 and _ld(x2) % vec == 0

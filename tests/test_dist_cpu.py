@@ -152,7 +152,8 @@ def _sliced_worker(rank, world, port, q, x_layout, row_groups):
         pl = g.plan
         assert pl.n_padded >= n and pl.blk * (world - 1) < n
         assert g.num_edges_local == int(((ei2[1] >= pl.g_lo) & (ei2[1] < pl.g_hi)).sum())
-        xin = g.slice_cols(x) if x_layout == 'cols' else g.local_rows(x).contiguous()
+        xin = {'cols': lambda: g.slice_cols(x), 'full': lambda: x,
+               'rows': lambda: g.local_rows(x).contiguous()}[x_layout]()
         out_local = sliced_gcn_forward(g, xin, layers, relu=True, x_layout=x_layout,
                                        aggregate=_sliced_oracle_aggregate,
                                        transform=_sliced_transform)
@@ -179,7 +180,8 @@ def _sliced_worker(rank, world, port, q, x_layout, row_groups):
 
 @pytest.mark.parametrize('world,x_layout,row_groups', [(2, 'cols', 1), (2, 'rows', 1),
                                                        (3, 'cols', 1), (4, 'cols', 2),
-                                                       (2, 'rows', 2)])
+                                                       (2, 'rows', 2), (2, 'full', 1),
+                                                       (4, 'full', 2)])
 def test_sliced_gcn_gloo(world, x_layout, row_groups):
     ctx = mp.get_context('spawn')
     q = ctx.Queue()
@@ -195,7 +197,8 @@ def test_sliced_gcn_gloo(world, x_layout, row_groups):
     assert status == 'ok', err
     assert err <= 1e-5, err
     # layout changes: one per aggregation (cols -> rows) + one per rows -> cols
-    assert ncoll == (7 if x_layout == 'cols' else 8) and nbytes > 0
+    # ('full' with an injected aggregate: the replicated input is column-sliced locally)
+    assert ncoll == (8 if x_layout == 'rows' else 7) and nbytes > 0
 
 
 def test_slice_plan_properties():
@@ -217,6 +220,11 @@ def test_slice_plan_properties():
                 assert Fp >= F and Fp == Fc * gc and Fc % 8 == 0 and Fp - F < 32 * gc
                 cover = [plans[0].col_slice(F, 4, c) for c in range(gc)]
                 assert cover[0].start == 0 and cover[-1].stop == Fp
+    # blk_align (peer transport): row blocks that split into equal row chunks
+    for n in (7, 301, 2449029):
+        pa = [SlicePlan(n, 8, r, 2, blk_align=8) for r in range(8)]
+        assert pa[0].blk % 8 == 0 and sum(p.n_local for p in pa) == n
+        assert pa[0].blk - SlicePlan(n, 8, 0, 2).blk < 8
     # exchange volume: P times less than the all-gather of the row partition
     p8 = SlicePlan(2449029, 8, 0)
     assert p8.exchange_bytes(256) * 8 <= 7 * p8.blk * 256 * 4 + 8

@@ -164,7 +164,7 @@ def _sliced_worker(rank, world, port, q, transport, x_layout, row_groups, fence=
             ok = torch.tensor([1.0 if rel <= 1e-6 else 0.0], device=dev)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)       # fail on every rank together
             assert float(ok) == 1.0, 'chunked pipeline changed the result: {:.3e}'.format(rel)
-            assert names.count('pygb_gemm_xw_routed') == chunks + 1, names
+            assert names.count('pygb_gemm_xw_routed') == chunks + 1, names       # both pipelines
         parts = [torch.zeros(pl.blk, 47, device=dev) for _ in range(world)]
         pad = torch.zeros(pl.blk, 47, device=dev)
         pad[:pl.n_local] = out_local
@@ -231,21 +231,22 @@ def test_sliced_gcn_one_gpu(transport, x_layout):
     _run_sliced(1, transport, x_layout)
 
 
-@pytest.mark.parametrize('chunks', [2, 8])
-def test_sliced_gcn_one_gpu_chunked_pipeline(chunks):
-    """world_size 1, peer transport: the chunked aggregate -> transform pipeline (two streams,
-    capped grids) on the rank's own arena; bit-identical to the unchunked forward."""
-    _run_sliced(1, 'peer', 'cols', fence='nccl', chunks=chunks)
+@pytest.mark.parametrize('x_layout,chunks', [('cols', 2), ('cols', 8), ('full', 2), ('full', 8)])
+def test_sliced_gcn_one_gpu_chunked_pipeline(x_layout, chunks):
+    """world_size 1, peer transport: the chunked aggregate -> transform pipelines (two streams,
+    capped grids) on the rank's own arena; same result as the unchunked forward."""
+    _run_sliced(1, 'peer', x_layout, fence='nccl', chunks=chunks)
 
 
-@pytest.mark.parametrize('row_groups,chunks', [(1, 2), (1, 4), (2, 4)])
-def test_sliced_gcn_two_gpus_chunked_pipeline(row_groups, chunks):
+@pytest.mark.parametrize('x_layout,row_groups,chunks', [('cols', 1, 2), ('cols', 1, 4), ('cols', 2, 4),
+                                                         ('full', 1, 4), ('full', 2, 2)])
+def test_sliced_gcn_two_gpus_chunked_pipeline(x_layout, row_groups, chunks):
     if torch.cuda.device_count() < 2:
         pytest.skip('needs two GPUs')
-    _run_sliced(2, 'peer', 'cols', row_groups, fence='nccl', chunks=chunks)
+    _run_sliced(2, 'peer', x_layout, row_groups, fence='nccl', chunks=chunks)
 
 
-@pytest.mark.parametrize('x_layout,chunks', [('cols', 1), ('cols', 4), ('full', 1)])
+@pytest.mark.parametrize('x_layout,chunks', [('cols', 1), ('cols', 4), ('full', 1), ('full', 4)])
 def test_sliced_gcn_eight_gpus_two_by_four(x_layout, chunks):
     """The layout the driver's 8-GPU SCALE run uses: 2 row groups x 4 column slices, peer stores
     ('full': the first aggregation over the rank's own rows from the replicated input)."""
