@@ -174,6 +174,26 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
                                   int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
                                   void* ws, size_t ws_bytes, pygb_stream_t s);
 
+/* pygb_seg_gather_reduce_stream WITHOUT a workspace argument and without any device
+ * allocation (no counterpart in the reference: added
+ * for callers that cannot call cudaMalloc — code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments, same kernels and
+ * bit-identical results; the fix-up scratch (partial rows + tail table) lives in ONE
+ * file-scope __device__ array of PYGB_SEG_STREAM_STATIC_WS_BYTES that every GPU loading
+ * the library holds until exit.  Returns PYGB_E_WORKSPACE (message names both sizes) when
+ * pygb_seg_stream_workspace(dtype, n_sub, F) exceeds that limit.  All calls on a device
+ * share the array, which keeps the previous call's contents (the entry point resets, on
+ * the stream, the part that must start clean): calls that overlap on the GPU — two
+ * streams, two threads — RACE; serialise them on one stream. */
+#define PYGB_SEG_STREAM_STATIC_WS_BYTES (16u << 20)
+int pygb_seg_gather_reduce_stream_static(int reduce, int dtype, const void* x, int64_t ldx,
+                                         int64_t F, const int32_t* rowptr,
+                                         const int32_t* idx_flagged, const float* edge_w,
+                                         const float* bias, int64_t n_rows, int64_t E,
+                                         const int32_t* nz_rows, const int32_t* sub_info,
+                                         int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
+                                         pygb_stream_t s);
+
 /* The same kernel with a routed output (feature-sliced multi-GPU aggregation,
  * DESIGN.md §4): destination row r is stored at
  *   (T*)out_tab[r / blk_rows] + (r % blk_rows) * ldo,

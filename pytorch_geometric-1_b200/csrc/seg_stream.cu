@@ -619,3 +619,65 @@ int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, i
 }
 
 }  // extern "C"
+
+// ---- no-allocation variant ---------------------------------------------------------------
+// The partial rows and tail table of the fix-up pass live in a file-scope device array instead
+// of a caller-provided workspace, for callers that cannot allocate (CUDA graph capture, serving
+// loops).  Every GPU that loads the library holds the array until exit.  In host code the
+// array's NAME is only a stand-in: the device address comes from cudaGetSymbolAddress, looked
+// up once per device with that device current.
+static __device__ __align__(256) unsigned char g_seg_static_ws[PYGB_SEG_STREAM_STATIC_WS_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_ws_mu;
+void* g_static_ws_ptr[kMaxDevices] = {};
+
+int static_ws_for_current_device(void** ptr) {
+  int dev = -1;
+  PYGB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("pygb_seg_gather_reduce_stream_static: device ordinal %d out of range", dev);
+    return PYGB_E_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_static_ws_mu);
+  if (!g_static_ws_ptr[dev]) {
+    void* p = nullptr;
+    PYGB_CUDA(cudaGetSymbolAddress(&p, g_seg_static_ws));
+    if (!p || (reinterpret_cast<uintptr_t>(p) & 255) != 0) {
+      set_error("pygb_seg_gather_reduce_stream_static: bad symbol address %p", p);
+      return PYGB_E_CUDA;
+    }
+    g_static_ws_ptr[dev] = p;
+  }
+  *ptr = g_static_ws_ptr[dev];
+  return PYGB_OK;
+}
+}  // namespace
+
+extern "C" int pygb_seg_gather_reduce_stream_static(
+    int reduce, int dtype, const void* x, int64_t ldx, int64_t F, const int32_t* rowptr,
+    const int32_t* idx_flagged, const float* edge_w, const float* bias, int64_t n_rows, int64_t E,
+    const int32_t* nz_rows, const int32_t* sub_info, int32_t Ts, int64_t n_sub, void* out,
+    int64_t ldo, pygb_stream_t s) {
+  PYGB_REQUIRE(out || n_rows == 0 || F == 0, "pygb_seg_gather_reduce_stream_static: null pointer");
+  PYGB_REQUIRE((dtype == PYGB_F32 || dtype == PYGB_BF16) && F >= 0 && n_sub >= 0 &&
+                   n_sub < (1ll << 31),
+               "pygb_seg_gather_reduce_stream_static: bad dtype / sizes");
+  const size_t need = pygb_seg_stream_workspace(dtype, n_sub, F);
+  if (need > (size_t)PYGB_SEG_STREAM_STATIC_WS_BYTES) {
+    set_error("pygb_seg_gather_reduce_stream_static: needs %zu bytes of scratch for n_sub=%lld, "
+              "F=%lld but the built-in array holds %zu; use pygb_seg_gather_reduce_stream with a "
+              "caller-provided workspace (or a plan with a larger Ts)",
+              need, (long long)n_sub, (long long)F, (size_t)PYGB_SEG_STREAM_STATIC_WS_BYTES);
+    return PYGB_E_WORKSPACE;
+  }
+  void* ws = nullptr;
+  int rc = static_ws_for_current_device(&ws);
+  if (rc) return rc;
+  // seg_stream_impl resets the tail table (0xff) on the stream before every launch and the
+  // fix-up pass reads only the partial rows that launch wrote: nothing else needs clearing
+  return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
+                         nz_rows, sub_info, Ts, n_sub, out, nullptr, 0, 0, ldo, 0, ws,
+                         (size_t)PYGB_SEG_STREAM_STATIC_WS_BYTES, s);
+}
