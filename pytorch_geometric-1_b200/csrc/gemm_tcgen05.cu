@@ -92,6 +92,20 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
       "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
+// One lane of the (converged) warp; the compiler keeps code predicated on it on the uniform
+// datapath, which `if (lane == 0)` does not (every UTCHMMA then sits in an ELECT / BRA.U.ANY
+// loop with R2UR moves: ~60 clocks of issue per MMA on the single issuing thread).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tcgen05_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -189,6 +203,8 @@ struct GemmParams {
                   // 8.6e-6 -> ~3e-6 of the largest entry against fp64).  Used when TMEM has room
                   // (2 buffers x 2 x MH*BN <= 512 columns).
   int m_tiles, n_tiles;
+  int dbg;                   // probe builds only (PYGB_GEMM_TS_DBG): wrong numbers, for timing
+  int ts_ra, ts_sb, ts_ta;   // gemm_ts_kernel: raw A tiles / W stages in shared memory, A stages in TMEM
   // routed output (row layout -> column layout fused into the epilogue): column block
   // q = col / c_fc of row r goes to c_tab[q * c_dup + d] + (c_row0 + r) * c_ldd + col % c_fc
   // for every d < c_dup (local or peer-GPU bases).  c_tab == nullptr: plain C.
@@ -196,6 +212,123 @@ struct GemmParams {
   int c_fc, c_dup;
   int64_t c_row0, c_ldd;
 };
+
+// Epilogue of one 32-lane quarter of a 128-row accumulator (lane = row): every thread reads 32
+// columns of its row from TMEM, the warp transposes the 32x32 block through its `epi` staging
+// area and writes full 128-byte lines (4 rows per instruction); bias / ReLU / bf16 conversion /
+// routed destinations are applied on the way out.  `tbase` = TMEM address of column 0 of the
+// accumulator (lane quarter included), `row0` = global row of lane 0 of this warp.
+template <int KIND>
+__device__ __forceinline__ void gemm_epilogue_rows(const GemmParams& P, uint32_t tbase, int BN,
+                                                   int acc_cols, bool split_acc, uint32_t epi,
+                                                   int row0, int n0, int lane, bool vec_ok) {
+  float* const Cf = static_cast<float*>(P.C);
+  __nv_bfloat16* const Cb = static_cast<__nv_bfloat16*>(P.C);
+  const int rr = lane >> 3, jj = lane & 7;
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    uint32_t r[32];
+    if (c0 + 32 <= BN) {
+      tmem_ld32(tbase + (uint32_t)c0, r);
+    } else {  // BN is a multiple of 16: a last half chunk
+      tmem_ld16(tbase + (uint32_t)c0, r);
+#pragma unroll
+      for (int j = 16; j < 32; ++j) r[j] = 0u;
+    }
+    tmem_ld_wait();
+    if (split_acc) {  // main + corrections, one round-to-nearest fp32 add
+      uint32_t r2[32];
+      if (c0 + 32 <= BN) {
+        tmem_ld32(tbase + (uint32_t)(acc_cols + c0), r2);
+      } else {
+        tmem_ld16(tbase + (uint32_t)(acc_cols + c0), r2);
+#pragma unroll
+        for (int j = 16; j < 32; ++j) r2[j] = 0u;
+      }
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+    }
+#pragma unroll
+    for (int j = 0; j < 32; j += 4)
+      asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(
+                       epi + (uint32_t)((lane * kEpiRowFloats + j) * 4)),
+                   "r"(r[j]), "r"(r[j + 1]), "r"(r[j + 2]), "r"(r[j + 3])
+                   : "memory");
+    __syncwarp();
+    const int col = n0 + c0 + jj * 4;
+    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (P.bias != nullptr) {
+      if (col < P.N) bv.x = __ldg(P.bias + col);
+      if (col + 1 < P.N) bv.y = __ldg(P.bias + col + 1);
+      if (col + 2 < P.N) bv.z = __ldg(P.bias + col + 2);
+      if (col + 3 < P.N) bv.w = __ldg(P.bias + col + 3);
+    }
+    const bool col_ok = col < P.N;
+    if (P.c_tab == nullptr) {       // plain C: the hot path stays branch-free inside the row loop
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int rl = i * 4 + rr;
+        float4 v;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
+        v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+        if (P.relu) {
+          v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
+          v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
+        }
+        const int row = row0 + rl;
+        if (row < P.M && col_ok && !(P.dbg & 4)) {
+          if (KIND == 1) {
+            __nv_bfloat16* dst = Cb + (int64_t)row * P.ldc + col;
+            if (vec_ok && col + 4 <= P.N) {     // 4 bf16 = 8 bytes, 8-byte aligned
+              *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+            } else {
+              dst[0] = __float2bfloat16_rn(v.x);
+              if (col + 1 < P.N) dst[1] = __float2bfloat16_rn(v.y);
+              if (col + 2 < P.N) dst[2] = __float2bfloat16_rn(v.z);
+              if (col + 3 < P.N) dst[3] = __float2bfloat16_rn(v.w);
+            }
+          } else {
+            float* dst = Cf + (int64_t)row * P.ldc + col;
+            if (vec_ok && col + 4 <= P.N) {
+              *reinterpret_cast<float4*>(dst) = v;
+            } else {
+              dst[0] = v.x;
+              if (col + 1 < P.N) dst[1] = v.y;
+              if (col + 2 < P.N) dst[2] = v.z;
+              if (col + 3 < P.N) dst[3] = v.w;
+            }
+          }
+        }
+      }
+    } else {                        // routed: N and c_fc are multiples of 4 -> whole vectors
+      const int qb = col_ok ? col / P.c_fc : 0;
+      const int64_t off = P.c_row0 * P.c_ldd + (col - qb * P.c_fc);
+      for (int d = 0; d < P.c_dup; ++d) {
+        float* rb = col_ok ? P.c_tab[qb * P.c_dup + d] + off : nullptr;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rl = i * 4 + rr;
+          float4 v;
+          asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                       : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
+          v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
+          if (P.relu) {
+            v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
+            v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
+          }
+          const int row = row0 + rl;
+          if (row < P.M && col_ok)
+            *reinterpret_cast<float4*>(rb + (int64_t)row * P.c_ldd) = v;
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
 
 // PASSES = 3: 3xTF32 split (fp32-faithful);  PASSES = 1: plain TF32.
 // Persistent: CTA b works on tiles b, b+grid, ...  (n fastest, so the A tile of a
@@ -297,8 +430,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer: the whole warp walks the loop, one elected lane issues =====
+    {
       // D fp32; A/B format 2 = tf32, 1 = bf16; both K-major
       constexpr uint32_t kFmt = KIND == 1 ? 1u : 2u;
       const uint32_t idesc = (1u << 4) | (kFmt << 7) | (kFmt << 10) | ((uint32_t)(BN >> 3) << 17) |
@@ -316,6 +449,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
           tcgen05_fence_after();
           const uint64_t dbh = SW64 ? smem_desc_sw64(b_hi(s)) : smem_desc_sw128(b_hi(s));
           const uint64_t dbl = SW64 ? smem_desc_sw64(b_lo(s)) : smem_desc_sw128(b_lo(s));
+          if (elect_one()) {
 #pragma unroll
           for (int h = 0; h < MH; ++h) {       // 128-row halves of the tile share the W stage
             const uint32_t hoff = (uint32_t)(h * kBM * kBK * kEsz);
@@ -335,8 +469,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
           }
           tcgen05_commit(empty(s));  // frees the stage once the MMAs have read it
+          }
+          __syncwarp();
         }
-        tcgen05_commit(acc_full(buf));  // accumulator of this tile complete
+        if (elect_one()) tcgen05_commit(acc_full(buf));  // accumulator of this tile complete
+        __syncwarp();
       }
     }
   } else if (warp < 6) {
@@ -381,9 +518,6 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const uint32_t epi = base + (uint32_t)S * stage_bytes + (uint32_t)(q * kEpiWarpBytes);
     const bool vec_ok = (P.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.C) & 15) == 0);
-    float* const Cf = static_cast<float*>(P.C);
-    __nv_bfloat16* const Cb = static_cast<__nv_bfloat16*>(P.C);
-    const int rr = lane >> 3, jj = lane & 7;
     int tl = 0;
     for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, ++tl) {
       const int m0 = (tile / P.n_tiles) * kTileM, n0 = (tile % P.n_tiles) * BN;
@@ -393,112 +527,333 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
       for (int h = 0; h < MH; ++h) {
       const int row0 = m0 + h * kBM + q * 32;
       const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * acc_stride + h * BN);
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        if (c0 + 32 <= BN) {
-          tmem_ld32(tbase + (uint32_t)c0, r);
-        } else {  // BN is a multiple of 16: a last half chunk
-          tmem_ld16(tbase + (uint32_t)c0, r);
-#pragma unroll
-          for (int j = 16; j < 32; ++j) r[j] = 0u;
-        }
-        tmem_ld_wait();
-        if (split_acc) {  // main + corrections, one round-to-nearest fp32 add
-          uint32_t r2[32];
-          if (c0 + 32 <= BN) {
-            tmem_ld32(tbase + (uint32_t)(acc_cols + c0), r2);
-          } else {
-            tmem_ld16(tbase + (uint32_t)(acc_cols + c0), r2);
-#pragma unroll
-            for (int j = 16; j < 32; ++j) r2[j] = 0u;
-          }
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
-        }
-#pragma unroll
-        for (int j = 0; j < 32; j += 4)
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(
-                           epi + (uint32_t)((lane * kEpiRowFloats + j) * 4)),
-                       "r"(r[j]), "r"(r[j + 1]), "r"(r[j + 2]), "r"(r[j + 3])
-                       : "memory");
-        __syncwarp();
-        const int col = n0 + c0 + jj * 4;
-        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (P.bias != nullptr) {
-          if (col < P.N) bv.x = __ldg(P.bias + col);
-          if (col + 1 < P.N) bv.y = __ldg(P.bias + col + 1);
-          if (col + 2 < P.N) bv.z = __ldg(P.bias + col + 2);
-          if (col + 3 < P.N) bv.w = __ldg(P.bias + col + 3);
-        }
-        const bool col_ok = col < P.N;
-        if (P.c_tab == nullptr) {       // plain C: the hot path stays branch-free inside the row loop
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int rl = i * 4 + rr;
-            float4 v;
-            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
-                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                         : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
-            v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
-            if (P.relu) {
-              v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
-              v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
-            }
-            const int row = row0 + rl;
-            if (row < P.M && col_ok) {
-              if (KIND == 1) {
-                __nv_bfloat16* dst = Cb + (int64_t)row * P.ldc + col;
-                if (vec_ok && col + 4 <= P.N) {     // 4 bf16 = 8 bytes, 8-byte aligned
-                  *reinterpret_cast<uint2*>(dst) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
-                } else {
-                  dst[0] = __float2bfloat16_rn(v.x);
-                  if (col + 1 < P.N) dst[1] = __float2bfloat16_rn(v.y);
-                  if (col + 2 < P.N) dst[2] = __float2bfloat16_rn(v.z);
-                  if (col + 3 < P.N) dst[3] = __float2bfloat16_rn(v.w);
-                }
-              } else {
-                float* dst = Cf + (int64_t)row * P.ldc + col;
-                if (vec_ok && col + 4 <= P.N) {
-                  *reinterpret_cast<float4*>(dst) = v;
-                } else {
-                  dst[0] = v.x;
-                  if (col + 1 < P.N) dst[1] = v.y;
-                  if (col + 2 < P.N) dst[2] = v.z;
-                  if (col + 3 < P.N) dst[3] = v.w;
-                }
-              }
-            }
-          }
-        } else {                        // routed: N and c_fc are multiples of 4 -> whole vectors
-          const int qb = col_ok ? col / P.c_fc : 0;
-          const int64_t off = P.c_row0 * P.c_ldd + (col - qb * P.c_fc);
-          for (int d = 0; d < P.c_dup; ++d) {
-            float* rb = col_ok ? P.c_tab[qb * P.c_dup + d] + off : nullptr;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int rl = i * 4 + rr;
-              float4 v;
-              asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
-                           : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                           : "r"(epi + (uint32_t)((rl * kEpiRowFloats + jj * 4) * 4)));
-              v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
-              if (P.relu) {
-                v.x = v.x < 0.f ? 0.f : v.x; v.y = v.y < 0.f ? 0.f : v.y;
-                v.z = v.z < 0.f ? 0.f : v.z; v.w = v.w < 0.f ? 0.f : v.w;
-              }
-              const int row = row0 + rl;
-              if (row < P.M && col_ok)
-                *reinterpret_cast<float4*>(rb + (int64_t)row * P.c_ldd) = v;
-            }
-          }
-        }
-        __syncwarp();
-      }
+        gemm_epilogue_rows<KIND>(P, tbase, BN, acc_cols, split_acc, epi, row0, n0, lane, vec_ok);
       }
       tcgen05_fence_before();
       mbar_arrive(acc_empty(buf));  // 128 arrivals: the MMA warp may overwrite this buffer
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
+                 "r"((uint32_t)P.tmem_cols)
+                 : "memory");
+  }
+}
+
+// ---- 3xTF32 with the A operand in TMEM ("TS" form of tcgen05.mma) -------------------------
+// The shared-memory port of an SM moves 128 bytes per clock, and in the kernel above every
+// k-step of 32 sends through it: the TMA fill (A + Wh + Wl), the splitter's read of A and its
+// writes of Ah and Al, and the operand reads of 12 MMAs (Ah twice, Al once, Wh twice, Wl once)
+// — 272 KB at BN = 256, i.e. ~2,100 clocks for 1,536 clocks of tensor work: the port, not HBM
+// and not the tensor pipe, paces that kernel (profiles/r02_k5_ts.md).  Here the splitter warps
+// read the raw fp32 tile once and write Ah / Al straight into TENSOR memory (tcgen05.st, lane =
+// row, 32 + 32 columns per stage), and the MMAs take A from there: per k-step only the fill and
+// the W reads touch shared memory (112 KB at BN = 128).  TMEM holds two accumulator buffers plus
+// the A ring (64 columns per stage), so BN <= 128: wider N runs as several n-tiles of one
+// 128-row block back to back on the same CTA (A comes from HBM once, then from L2).
+// Same products, same accumulation order per output element as gemm_tf32_kernel<3, 1, 32>.
+__device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0],"
+      " {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+      "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+      "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+      "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]),
+      "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]),
+      "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+constexpr int kTsACols = 2 * kBK;   // TMEM columns of one A stage: Ah (32) + Al (32)
+constexpr int kTsThreads = 352;     // + warp 10: the W producer
+constexpr int kTsMaxRA = 12;        // raw A tiles in flight (16 KB each)
+constexpr int kTsMaxSB = 6;         // W stages (Wh + Wl tiles of BN x 32)
+
+// Probe (PYGB_GEMM_TS_DBG & 16): clocks CTA 0 spends in each wait, per role.
+static __device__ unsigned long long g_ts_prof[16];
+static __device__ unsigned long long g_ts_cta[2 * 160];   // per CTA: clocks, ns
+__device__ __forceinline__ void mbar_wait_prof(uint32_t bar, uint32_t parity, bool prof,
+                                               unsigned long long& acc) {
+  if (!prof) {
+    mbar_wait(bar, parity);
+    return;
+  }
+  const long long t0 = clock64();
+  mbar_wait(bar, parity);
+  acc += (unsigned long long)(clock64() - t0);
+}
+
+// Three rings, because the three streams have different latencies: raw A tiles come from HBM
+// (~3 us under load: an SM needs >= 100 KB of loads in flight to stream at its share of the HBM
+// rate, and the raw tile is all that has to wait that long), W tiles come from L2, and the split
+// A lives in TMEM for the short splitter -> MMA hop.
+//   rawA[RA]  : warp 0 (TMA) -> a_full  -> splitter (reads into registers) -> a_empty
+//   W[SB]     : warp 10 (TMA) -> b_full -> MMA ........ tcgen05.commit -> b_empty
+//   tmemA[SB] : splitter (tcgen05.st) -> ready -> MMA .. (the same commit: both rings have depth
+//               SB and move in lock step, so b_empty has two waiters: warp 10 and the splitter)
+__global__ void __launch_bounds__(kTsThreads, 1)
+gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBh,
+               const __grid_constant__ CUtensorMap mapBl, const GemmParams P) {
+  extern __shared__ __align__(1024) unsigned char gsm[];
+  __shared__ __align__(8) uint64_t bars[2 * kTsMaxRA + 3 * kTsMaxSB + 4];
+  __shared__ uint32_t tmem_base_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int BN = P.BN, RA = P.ts_ra, SB = P.ts_sb, TA = P.ts_ta;
+  const uint32_t b_bytes = (uint32_t)BN * kBK * 4;
+  const uint32_t base = (smem_u32(gsm) + 1023u) & ~1023u;
+  const uint32_t b_base = base + (uint32_t)RA * kATileBytes;
+  auto a_raw = [&](int s) { return base + (uint32_t)s * kATileBytes; };
+  auto b_hi = [&](int s) { return b_base + (uint32_t)s * 2u * b_bytes; };
+  auto b_lo = [&](int s) { return b_hi(s) + b_bytes; };
+  const uint32_t bar0 = smem_u32(bars);
+  auto a_full = [&](int s) { return bar0 + 8u * s; };
+  auto a_empty = [&](int s) { return bar0 + 8u * (kTsMaxRA + s); };
+  auto b_full = [&](int s) { return bar0 + 8u * (2 * kTsMaxRA + s); };
+  auto b_empty = [&](int s) { return bar0 + 8u * (2 * kTsMaxRA + kTsMaxSB + s); };
+  auto ready = [&](int s) { return bar0 + 8u * (2 * kTsMaxRA + 2 * kTsMaxSB + s); };
+  auto acc_full = [&](int b) { return bar0 + 8u * (2 * kTsMaxRA + 3 * kTsMaxSB + b); };
+  auto acc_empty = [&](int b) {
+    return bar0 + 8u * (2 * kTsMaxRA + 3 * kTsMaxSB + 2 + b);
+  };
+
+  // ring position + phase, advanced without divisions (these loops run on single threads)
+  struct Ring {
+    int s;
+    uint32_t ph;
+    __device__ __forceinline__ void next(int depth) {
+      if (++s == depth) {
+        s = 0;
+        ph ^= 1u;
+      }
+    }
+  };
+  const int nk = (P.K + kBK - 1) / kBK;
+  const bool split_acc = P.split_acc != 0;
+  const int acc_stride = BN * (split_acc ? 2 : 1);
+  const uint32_t a_col0 = (uint32_t)(2 * acc_stride);   // the A ring follows the two accumulators
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < RA; ++s) {
+      mbar_init(a_full(s), 1);
+      mbar_init(a_empty(s), 4);    // one arrival per splitter warp
+    }
+    for (int s = 0; s < SB; ++s) {
+      mbar_init(b_full(s), 1);
+      mbar_init(b_empty(s), 1);
+    }
+    for (int s = 0; s < TA; ++s) {
+      mbar_init(ready(s), 4);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(acc_full(b), 1);
+      mbar_init(acc_empty(b), 4);  // one per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(&tmem_base_s)),
+                 "r"((uint32_t)P.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_d = tmem_base_s;
+  // every role walks the same sequence of k-steps: 128-row blocks b, b + grid, ...; all n-tiles
+  // of a block back to back (the block's A tiles come from HBM once, then from L2)
+  const int my_blocks = P.m_tiles > (int)blockIdx.x
+                            ? (P.m_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int n_tiles_cta = my_blocks * P.n_tiles;
+  const bool prof = (P.dbg & 16) && blockIdx.x == 0;
+  unsigned long long w0 = 0, w1 = 0, w2 = 0;
+  const long long t_begin = clock64();
+  unsigned long long t_begin_ns = 0;
+  if (P.dbg & 16) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_begin_ns));
+
+  if (warp == 0) {
+    // ===== raw A producer =====
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+      Ring ra{0, 0u};
+      for (int mb = blockIdx.x; mb < P.m_tiles; mb += gridDim.x) {
+        const int m0 = mb * kBM;
+        for (int kk = 0, kt = 0; kk < P.n_tiles * nk; ++kk, kt = kt + 1 == nk ? 0 : kt + 1, ra.next(RA)) {
+          const int s = ra.s;
+          mbar_wait_prof(a_empty(s), ra.ph ^ 1u, prof, w0);
+          mbar_expect_tx(a_full(s), kATileBytes);
+          const int kcol = kt * kBK;
+          if (P.a_3d) {
+            const int sl = kcol / P.a_kw;
+            tma_load_3d(a_raw(s), &mapA, a_full(s), kcol - sl * P.a_kw, m0, sl);
+          } else {
+            tma_load_2d(a_raw(s), &mapA, a_full(s), kcol, m0);
+          }
+        }
+      }
+      if (prof) { g_ts_prof[0] = w0; g_ts_prof[1] = (unsigned long long)(clock64() - t_begin); }
+    }
+  } else if (warp == 10) {
+    // ===== W producer =====
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBh) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBl) : "memory");
+      Ring rb{0, 0u};
+      for (int tl = 0, nt = 0; tl < n_tiles_cta; ++tl, nt = nt + 1 == P.n_tiles ? 0 : nt + 1) {
+        const int n0 = nt * BN;
+        for (int kt = 0; kt < nk; ++kt, rb.next(SB)) {
+          const int s = rb.s;
+          mbar_wait_prof(b_empty(s), rb.ph ^ 1u, prof, w0);
+          mbar_expect_tx(b_full(s), 2 * b_bytes);
+          tma_load_2d(b_hi(s), &mapBh, b_full(s), kt * kBK, n0);
+          tma_load_2d(b_lo(s), &mapBl, b_full(s), kt * kBK, n0);
+        }
+      }
+      if (prof) { g_ts_prof[2] = w0; g_ts_prof[3] = (unsigned long long)(clock64() - t_begin); }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: A from TMEM, W from shared memory.  The whole warp walks the loop
+    // (uniform control flow); one elected lane issues =====
+    {
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                             ((uint32_t)(kBM >> 4) << 24);
+      Ring rb{0, 0u};
+      for (int tl = 0; tl < n_tiles_cta; ++tl) {
+        const int buf = tl & 1;
+        mbar_wait_prof(acc_empty(buf), ((uint32_t)(tl >> 1) & 1u) ^ 1u, prof, w0);
+        tcgen05_fence_after();
+        const uint32_t dc = tmem_d + (uint32_t)(buf * acc_stride);
+        const uint32_t dcc = split_acc ? dc + (uint32_t)BN : dc;
+        for (int kt = 0; kt < nk; ++kt, rb.next(SB)) {
+          const int sb = rb.s, ta = rb.s;
+          mbar_wait_prof(b_full(sb), rb.ph, prof, w1);
+          mbar_wait_prof(ready(ta), rb.ph, prof, w2);
+          tcgen05_fence_after();
+          const uint64_t dbh = smem_desc_sw128(b_hi(sb));
+          const uint64_t dbl = smem_desc_sw128(b_lo(sb));
+          const uint32_t ah = tmem_d + a_col0 + (uint32_t)(ta * kTsACols);
+          const uint32_t al = ah + (uint32_t)kBK;
+          if (elect_one()) {
+#pragma unroll
+            for (int k = 0; k < kBK / 8; ++k) {   // UMMA_K = 8 tf32: 8 TMEM columns / 32 bytes of W
+              const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
+              mma_tf32_ts(dc, ah + 8u * k, dbh + 2u * k, idesc, acc);
+              if (P.dbg & 1) continue;
+              mma_tf32_ts(dcc, al + 8u * k, dbh + 2u * k, idesc, split_acc ? acc : 1u);
+              mma_tf32_ts(dcc, ah + 8u * k, dbl + 2u * k, idesc, 1u);
+            }
+            tcgen05_commit(b_empty(sb));   // W stage and TMEM A stage (same ring position) are free
+          }
+          __syncwarp();
+        }
+        if (elect_one()) tcgen05_commit(acc_full(buf));
+        __syncwarp();
+      }
+      if (prof && lane == 0) {
+        g_ts_prof[4] = w0; g_ts_prof[5] = w1; g_ts_prof[6] = w2;
+        g_ts_prof[7] = (unsigned long long)(clock64() - t_begin);
+        g_ts_prof[14] = g_ts_prof[15] = 0;
+      }
+    }
+  } else if (warp < 6) {
+    // ===== splitter: warps 2..5, thread = tile row = TMEM lane (warp % 4 = lane quarter) =====
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const uint32_t ta0 = tmem_d + ((uint32_t)(q * 32) << 16) + a_col0;
+    const uint32_t sw = (uint32_t)(row & 7);
+    const int n_steps = n_tiles_cta * nk;
+    Ring ra{0, 0u}, rt{0, 0u};
+    for (int it = 0; it < n_steps; ++it, ra.next(RA), rt.next(TA)) {
+      const int sa = ra.s, ta = rt.s;
+      mbar_wait_prof(a_full(sa), ra.ph, prof, w0);
+      const uint32_t src = a_raw(sa) + (uint32_t)row * 128u;
+      uint32_t hi[32], lo[32];
+      if (P.dbg & 2) {
+#pragma unroll
+        for (int c = 0; c < 32; ++c) hi[c] = lo[c] = 0u;
+      } else
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {   // 16-byte chunk c of the row sits at chunk c ^ (row % 8)
+        float4 v;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                     : "r"(src + (((uint32_t)c ^ sw) << 4)));
+        const float hx = round_tf32(v.x), hy = round_tf32(v.y);
+        const float hz = round_tf32(v.z), hw = round_tf32(v.w);
+        hi[4 * c + 0] = __float_as_uint(hx); hi[4 * c + 1] = __float_as_uint(hy);
+        hi[4 * c + 2] = __float_as_uint(hz); hi[4 * c + 3] = __float_as_uint(hw);
+        lo[4 * c + 0] = __float_as_uint(round_tf32(v.x - hx));
+        lo[4 * c + 1] = __float_as_uint(round_tf32(v.y - hy));
+        lo[4 * c + 2] = __float_as_uint(round_tf32(v.z - hz));
+        lo[4 * c + 3] = __float_as_uint(round_tf32(v.w - hw));
+      }
+      mbar_wait_prof(b_empty(ta), rt.ph ^ 1u, prof, w1);   // MMAs that read this stage are done
+      tcgen05_fence_after();
+      if (!(P.dbg & 8)) {
+        tmem_st32(ta0 + (uint32_t)(ta * kTsACols), hi);
+        tmem_st32(ta0 + (uint32_t)(ta * kTsACols + kBK), lo);
+      }
+      // the stores consumed every register the loads filled: the raw tile may be refilled.
+      // One arrival per warp (128 arrivals on one mbarrier serialise: ~1,000 clocks per k-step)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_empty(sa));
+      tmem_st_wait();
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ready(ta));
+    }
+    if (prof && threadIdx.x == 64) {
+      g_ts_prof[8] = w0; g_ts_prof[9] = w1;
+      g_ts_prof[10] = (unsigned long long)(clock64() - t_begin);
+    }
+  } else {
+    // ===== epilogue: warps 6..9 =====
+    const int q = warp & 3;
+    const uint32_t epi = b_base + (uint32_t)SB * 2u * b_bytes + (uint32_t)(q * kEpiWarpBytes);
+    const bool vec_ok = (P.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.C) & 15) == 0);
+    for (int tl = 0, nt = 0, mb = blockIdx.x; tl < n_tiles_cta; ++tl) {
+      const int buf = tl & 1;
+      mbar_wait_prof(acc_full(buf), (uint32_t)(tl >> 1) & 1u, prof, w0);
+      tcgen05_fence_after();
+      const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * acc_stride);
+      gemm_epilogue_rows<0>(P, tbase, BN, BN, split_acc, epi, mb * kBM + q * 32, nt * BN, lane,
+                            vec_ok);
+      if (++nt == P.n_tiles) {
+        nt = 0;
+        mb += gridDim.x;
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty(buf));
+    }
+    if ((P.dbg & 16) && threadIdx.x == 192 && blockIdx.x < 160) {
+      unsigned long long ns;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns));
+      g_ts_cta[2 * blockIdx.x] = (unsigned long long)(clock64() - t_begin);
+      g_ts_cta[2 * blockIdx.x + 1] = ns - t_begin_ns;
+    }
+    if (prof && threadIdx.x == 192) {
+      g_ts_prof[11] = w0; g_ts_prof[12] = (unsigned long long)(clock64() - t_begin);
+      g_ts_prof[13] = (unsigned long long)n_tiles_cta * (unsigned long long)nk;
     }
   }
   tcgen05_fence_before();
@@ -725,8 +1080,8 @@ gemm_xtg_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: A = X^T and B = G, both MN-major =====
-    if (lane == 0) {
+    // ===== MMA issuer: A = X^T and B = G, both MN-major (whole warp walks, one lane issues) =====
+    {
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) |
                              ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
       int it = 0;
@@ -741,6 +1096,7 @@ gemm_xtg_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
           const uint32_t ph = (uint32_t)(it / S) & 1u;
           mbar_wait(PASSES == 3 ? ready(s) : full(s), ph);
           tcgen05_fence_after();
+          if (elect_one()) {
 #pragma unroll
           for (int j = 0; j < kTRows / 8; ++j) {   // MMA k-steps of 8 rows = two 4-row atoms, 1024 bytes apart
             const uint64_t dgh = smem_desc_mn_sw128_32b(g_hi(s) + j * 1024u, kBoxBytes);
@@ -758,8 +1114,11 @@ gemm_xtg_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
             }
           }
           tcgen05_commit(empty(s));
+          }
+          __syncwarp();
         }
-        tcgen05_commit(acc_full(buf));
+        if (elect_one()) tcgen05_commit(acc_full(buf));
+        __syncwarp();
       }
     }
   } else if (warp < 6) {
@@ -952,6 +1311,8 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
     PYGB_LAUNCH_CHECK();
   }
   GemmParams P;
+  P.dbg = 0;
+  P.ts_ra = P.ts_sb = P.ts_ta = 0;
   P.bias = bias;
   P.relu = relu != 0;
   P.c_tab = route ? route->tab : nullptr;
@@ -987,6 +1348,90 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
       mh = tm / 128;
       bk = tk;
     }
+  }
+  // 3xTF32 default: the kernel that keeps Ah / Al in tensor memory (gemm_ts_kernel).
+  // PYGB_GEMM_TS=0 or an explicit PYGB_GEMM_TILE selects the shared-memory-operand kernels.
+  bool use_ts = passes == 3 && getenv("PYGB_GEMM_TILE") == nullptr;
+  if (const char* e = getenv("PYGB_GEMM_TS")) use_ts = use_ts && atoi(e) != 0;
+  if (use_ts) {
+    // BN <= 128 (TMEM: two accumulators + the A ring).  The correction terms get their own
+    // accumulator (split_acc) when 4*BN + the ring fit: BN <= 64, also chosen for N <= 128 with a
+    // long K, where the truncating accumulator matters (see GemmParams::split_acc).
+    int nt = (int)ceil_div(Np, 128);
+    if (Np > 64 && Np <= 128 && K > 256) nt = 2;
+    P.n_tiles = nt;
+    P.BN = round_up((int)ceil_div(Np, nt), 16);
+    P.split_acc = P.BN <= 64 ? 1 : 0;
+    if (const char* e = getenv("PYGB_GEMM_SPLIT_ACC")) P.split_acc = P.split_acc && atoi(e) != 0;
+    const int acc_stride = P.BN * (P.split_acc ? 2 : 1);
+    P.acc_bufs = 2;
+    P.m_tiles = (int)ceil_div(M, kBM);
+    // ring depths: TMEM stages from what the accumulators leave; W stages (L2 latency) 3, or 4
+    // when the tiles are small; every remaining 16 KB of shared memory is a raw A tile in flight
+    const int nk = (int)ceil_div(K, kBK);
+    const size_t b_stage = 2 * (size_t)P.BN * kBK * 4;
+    const size_t budget = 226 * 1024 - 1024 - kEpiBytes;
+    int ta = (512 - 2 * acc_stride) / kTsACols;
+    int sb = 4;
+    if (const char* e = getenv("PYGB_GEMM_TS_SB")) sb = atoi(e);
+    if (sb > ta) sb = ta;
+    if (sb > kTsMaxSB) sb = kTsMaxSB;
+    while (sb > 2 && (budget - sb * b_stage) / kATileBytes < 4) --sb;   // keep >= 4 raw A tiles
+    if (sb < 2) sb = 2;
+    ta = sb;
+    int ra = (int)((budget - sb * b_stage) / kATileBytes);
+    if (const char* e = getenv("PYGB_GEMM_TS_RA")) ra = ra < atoi(e) ? ra : atoi(e);
+    if (ra > kTsMaxRA) ra = kTsMaxRA;
+    PYGB_REQUIRE(ta >= 2 && ra >= 2, "pygb_gemm_xw: tile does not fit shared / tensor memory");
+    P.dbg = 0;
+    if (const char* e = getenv("PYGB_GEMM_TS_DBG")) P.dbg = atoi(e);
+    P.ts_ra = ra;
+    P.ts_sb = sb;
+    P.ts_ta = ta;
+    P.stages = sb;
+    int tc = 32;
+    while (tc < 2 * acc_stride + ta * kTsACols) tc <<= 1;
+    P.tmem_cols = tc;
+    const size_t smem = ra * (size_t)kATileBytes + sb * b_stage + kEpiBytes + 1024;
+    (void)nk;
+    CUtensorMap mapA, mapBh, mapBl;
+    int rc = a_slices > 1 ? make_map_a(&mapA, A, M, a_kw, lda, a_slices, a_plane, kBM, kBK)
+                          : make_map(&mapA, A, M, K, lda, kBM, kBK);
+    if (rc) return rc;
+    rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN, kBK);
+    if (rc) return rc;
+    rc = make_map(&mapBl, Wl, Np, Kp, Kp, P.BN, kBK);
+    if (rc) return rc;
+    int64_t ctas = P.m_tiles < sms ? P.m_tiles : sms;
+    if (route && route->max_ctas > 0 && ctas > route->max_ctas) ctas = route->max_ctas;
+    PYGB_CUDA(cudaFuncSetAttribute(gemm_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(226 * 1024)));
+    gemm_ts_kernel<<<(unsigned)ctas, kTsThreads, smem, st>>>(mapA, mapBh, mapBl, P);
+    PYGB_LAUNCH_CHECK();
+    if (P.dbg & 16) {   // probe: synchronises and prints CTA 0's wait clocks
+      unsigned long long h[16], hc[2 * 160];
+      PYGB_CUDA(cudaStreamSynchronize(st));
+      PYGB_CUDA(cudaMemcpyFromSymbol(h, g_ts_prof, sizeof(h)));
+      PYGB_CUDA(cudaMemcpyFromSymbol(hc, g_ts_cta, sizeof(hc)));
+      {
+        unsigned long long cmin = ~0ull, cmax = 0, nmin = ~0ull, nmax = 0;
+        for (int i = 0; i < (int)ctas && i < 160; ++i) {
+          if (hc[2 * i] < cmin) cmin = hc[2 * i];
+          if (hc[2 * i] > cmax) cmax = hc[2 * i];
+          if (hc[2 * i + 1] < nmin) nmin = hc[2 * i + 1];
+          if (hc[2 * i + 1] > nmax) nmax = hc[2 * i + 1];
+        }
+        fprintf(stderr, "[ts prof] per-CTA clocks min %llu max %llu, ns min %llu max %llu (CTA0 %llu clk %llu ns)\n",
+                cmin, cmax, nmin, nmax, hc[0], hc[1]);
+      }
+      fprintf(stderr,
+              "[ts prof] M=%d K=%d N=%d BN=%d ra=%d sb=%d ta=%d steps=%llu | A-prod wait a_empty %llu of %llu"
+              " | W-prod wait b_empty %llu of %llu | MMA wait acc_empty %llu b_full %llu ready %llu of"
+              " %llu (mma issue %llu, commits %llu) | split wait a_full %llu b_empty %llu of %llu | epi wait acc_full %llu of %llu\n",
+              P.M, P.K, P.N, P.BN, ra, sb, ta, h[13], h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7],
+              h[14], h[15], h[8], h[9], h[10], h[11], h[12]);
+    }
+    return PYGB_OK;
   }
   const int acc_cols = mh * P.BN;
   P.split_acc = (passes == 3 && 4 * acc_cols <= 512) ? 1 : 0;
@@ -1142,6 +1587,8 @@ int pygb_gemm_xw_bf16(const void* A, int64_t lda, int64_t M, int64_t K, const vo
     PYGB_LAUNCH_CHECK();
   }
   GemmParams P;
+  P.dbg = 0;
+  P.ts_ra = P.ts_sb = P.ts_ta = 0;
   P.bias = bias;
   P.relu = relu != 0;
   P.c_tab = nullptr;

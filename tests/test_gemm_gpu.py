@@ -85,6 +85,13 @@ def test_gemm_tile_shapes_agree(dev, monkeypatch, M, K, N):
         got = ops.gemm_xw_raw(x, w, b, relu=True)
         got1 = ops.gemm_xw_raw(x, w, None, passes=1)
         assert torch.equal(got, ref) and torch.equal(got1, ref1), tile
+    # the default 3xTF32 kernel (Ah / Al in tensor memory, BN <= 128, several n-tiles per row
+    # block) runs the same products in the same order per output element
+    monkeypatch.delenv('PYGB_GEMM_TILE')
+    assert torch.equal(ops.gemm_xw_raw(x, w, b, relu=True), ref), 'A-in-TMEM kernel'
+    monkeypatch.setenv('PYGB_GEMM_TS', '0')
+    assert torch.equal(ops.gemm_xw_raw(x, w, b, relu=True), ref), 'PYGB_GEMM_TS=0'
+    monkeypatch.delenv('PYGB_GEMM_TS')
     assert _rel(ops.gemm_xw_raw(x, w, b), x.double().cpu() @ w.double().cpu() + b.double().cpu()) <= 1e-5
 
 

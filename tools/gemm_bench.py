@@ -68,7 +68,7 @@ def main():
             out = fn()
             if ref is None:
                 ref = out
-            err = (out - ref).abs().max().item() / ref.abs().max().item()
+            err = (out - ref).abs().max().item() / max(ref.abs().max().item(), 1e-30)
             flops = 2.0 * M * K * N
             bytes_ = 4.0 * (M * K + M * N)
             print(json.dumps({'shape': name, 'M': M, 'K': K, 'N': N, 'kernel': kind,
