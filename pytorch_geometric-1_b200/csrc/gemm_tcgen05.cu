@@ -203,6 +203,7 @@ struct GemmParams {
                   // 8.6e-6 -> ~3e-6 of the largest entry against fp64).  Used when TMEM has room
                   // (2 buffers x 2 x MH*BN <= 512 columns).
   int m_tiles, n_tiles;
+  int tma_store;             // gemm_ts_kernel: the epilogue stores C with TMA (plain, 16-byte aligned C)
   int dbg;                   // probe builds only (PYGB_GEMM_TS_DBG): wrong numbers, for timing
   int ts_ra, ts_sb, ts_ta;   // gemm_ts_kernel: raw A tiles / W stages in shared memory, A stages in TMEM
   // routed output (row layout -> column layout fused into the epilogue): column block
@@ -583,7 +584,7 @@ __device__ __forceinline__ void tmem_st_wait() {
 }
 
 constexpr int kTsACols = 2 * kBK;   // TMEM columns of one A stage: Ah (32) + Al (32)
-constexpr int kTsThreads = 352;     // + warp 10: the W producer
+constexpr int kTsThreads = 480;     // + warp 10: the W producer, warps 11..14: second splitter group
 constexpr int kTsMaxRA = 12;        // raw A tiles in flight (16 KB each)
 constexpr int kTsMaxSB = 6;         // W stages (Wh + Wl tiles of BN x 32)
 
@@ -609,15 +610,195 @@ __device__ __forceinline__ void mbar_wait_prof(uint32_t bar, uint32_t parity, bo
 //   W[SB]     : warp 10 (TMA) -> b_full -> MMA ........ tcgen05.commit -> b_empty
 //   tmemA[SB] : splitter (tcgen05.st) -> ready -> MMA .. (the same commit: both rings have depth
 //               SB and move in lock step, so b_empty has two waiters: warp 10 and the splitter)
+// ---- epilogue with TMA stores --------------------------------------------------------------
+// The transposing epilogue above spends ~1,200 clocks per 32x32 block and warp on its dependent
+// ld.shared -> bias -> st.global chain (measured without the stores: gemm_ts_kernel was waiting for
+// its epilogue 98 % of the time at N = 256).  Here a thread keeps its row: bias / ReLU on the 32
+// registers, eight 16-byte st.shared into a 128-byte-swizzled 32x32 block, and one lane hands the
+// block to the TMA engine (cp.async.bulk.tensor store; rows >= M and columns >= N are clipped by
+// the tensor map).  Two staging blocks per warp: the store of one block overlaps the next.
+constexpr int kEpiTmaWarpBytes = 2 * 4096;
+constexpr int kEpiTmaBytes = 4 * kEpiTmaWarpBytes;
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
+               "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {   // <= N groups still reading shared memory
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// `stage` = this warp's two 4 KB staging blocks (1024-byte aligned); `blk` counts the blocks this
+// warp has stored so far (selects the staging block; carried across tiles).
+struct EpiProf {   // probe: clocks in tmem wait + math, staging wait, st.shared + fence, store issue
+  bool on;
+  unsigned long long a, b, c, d;
+};
+
+// one 32-row x 32-column block held in r[] (thread = row): bias, ReLU, staging, TMA store
+__device__ __forceinline__ void epi_store_block(const GemmParams& P, const CUtensorMap* mapC,
+                                                uint32_t (&r)[32], uint32_t stage, int row0, int col0,
+                                                int lane, int& blk, EpiProf& pf, long long t0) {
+  if (P.bias != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float b = col0 + j < P.N ? __ldg(P.bias + col0 + j) : 0.f;   // same address in every lane
+      r[j] = __float_as_uint(__uint_as_float(r[j]) + b);
+    }
+  }
+  if (P.relu) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const float v = __uint_as_float(r[j]);
+      r[j] = __float_as_uint(v < 0.f ? 0.f : v);
+    }
+  }
+  const uint32_t dst = stage + (uint32_t)((blk & 1) * 4096);
+  const uint32_t sw = (uint32_t)(lane & 7);
+  const long long t1 = pf.on ? clock64() : 0;
+  // the store that read this staging block two blocks ago has finished reading it (elect.sync
+  // picks the same lane of a full warp every time: the lane that issued that store)
+  if (elect_one()) tma_store_wait_read<1>();
+  __syncwarp();
+  const long long t2 = pf.on ? clock64() : 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(
+                     dst + (uint32_t)lane * 128u + (((uint32_t)j ^ sw) << 4)),
+                 "r"(r[4 * j]), "r"(r[4 * j + 1]), "r"(r[4 * j + 2]), "r"(r[4 * j + 3])
+                 : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
+  const long long t3 = pf.on ? clock64() : 0;
+  if (elect_one()) {
+    if (!(P.dbg & 4)) {
+      tma_store_2d(mapC, dst, col0, row0);
+      tma_store_commit();
+    }
+  }
+  ++blk;
+  if (pf.on) {
+    pf.a += (unsigned long long)(t1 - t0);
+    pf.b += (unsigned long long)(t2 - t1);
+    pf.c += (unsigned long long)(t3 - t2);
+    pf.d += (unsigned long long)(clock64() - t3);
+  }
+}
+
+__device__ __forceinline__ void epi_tmem_load(uint32_t taddr, bool full, uint32_t (&r)[32]) {
+  if (full) tmem_ld32(taddr, r);
+  else tmem_ld16(taddr, r);   // BN is a multiple of 16: a last half block
+}
+
+__device__ __forceinline__ void gemm_epilogue_rows_tma(const GemmParams& P, const CUtensorMap* mapC,
+                                                       uint32_t tbase, int BN, int acc_cols,
+                                                       bool split_acc, uint32_t stage, int row0,
+                                                       int n0, int lane, int& blk, EpiProf& pf) {
+  const int c_end = BN < P.N - n0 ? BN : P.N - n0;   // columns of this tile that exist
+  // (the TMEM load is not software-pipelined across blocks: registers named by an in-flight
+  // tcgen05.ld must not be touched before tcgen05.wait::ld, and under register pressure the
+  // compiler spilled them right after the load)
+  for (int c0 = 0; c0 < c_end; c0 += 32) {
+    const long long t0 = pf.on ? clock64() : 0;
+    const bool full = c0 + 32 <= BN;
+    uint32_t r[32];
+    epi_tmem_load(tbase + (uint32_t)c0, full, r);
+    tmem_ld_wait();
+    if (split_acc) {   // main + corrections, one round-to-nearest fp32 add
+      uint32_t r2[32];
+      epi_tmem_load(tbase + (uint32_t)(acc_cols + c0), full, r2);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+    }
+    if (!full) {
+#pragma unroll
+      for (int j = 16; j < 32; ++j) r[j] = 0u;
+    }
+    epi_store_block(P, mapC, r, stage, row0, n0 + c0, lane, blk, pf, t0);
+  }
+}
+
+// ---- CTA pairs (cta_group::2) ------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::
+                   : "memory");
+}
+// shared::cluster address of the same shared-memory location in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load whose bytes are counted on a barrier of the pair's leader CTA (`bar` = its
+// shared::cluster address); the tile lands in this CTA's shared memory
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                                 int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+// completion of the pair's MMAs arrives on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void tcgen05_commit_pair(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
+      " [%0], %1;" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void mma_tf32_ts_pair(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                                 uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// CG = 2: two CTAs of a cluster (the two SMs of a TPC) work on 256 rows as ONE tensor-core
+// operation (cta_group::2, M = 256): each CTA loads, splits and keeps in TMEM its own 128 rows
+// of A and drains its own 128 accumulator rows, but holds only HALF of every W tile (BN/2 rows
+// of Wh and of Wl) — the tensor cores of both SMs read both halves.  That halves the W fill and
+// the W operand reads per CTA, which is what the shared-memory port was short of
+// (profiles/r02_k5_ts.md).  The leader (cluster rank 0) issues every MMA; its b_full barrier
+// counts the TMA bytes of both CTAs, its `ready` / `acc_empty` barriers take the arrivals of both
+// CTAs' splitter / epilogue warps, and its commits arrive on b_empty / acc_full of both CTAs.
+template <int CG, bool PROF>   // PROF: the PYGB_GEMM_TS_DBG & 16 probe build (extra live registers)
 __global__ void __launch_bounds__(kTsThreads, 1)
 gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBh,
-               const __grid_constant__ CUtensorMap mapBl, const GemmParams P) {
+               const __grid_constant__ CUtensorMap mapBl, const __grid_constant__ CUtensorMap mapC,
+               const GemmParams P) {
   extern __shared__ __align__(1024) unsigned char gsm[];
   __shared__ __align__(8) uint64_t bars[2 * kTsMaxRA + 3 * kTsMaxSB + 4];
   __shared__ uint32_t tmem_base_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int BN = P.BN, RA = P.ts_ra, SB = P.ts_sb, TA = P.ts_ta;
-  const uint32_t b_bytes = (uint32_t)BN * kBK * 4;
+  const uint32_t b_bytes = (uint32_t)(BN / CG) * kBK * 4;   // this CTA's part of a W tile
+  const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
+  const int unit0 = (int)blockIdx.x / CG, ustride = (int)gridDim.x / CG;   // units of CG*128 rows
   const uint32_t base = (smem_u32(gsm) + 1023u) & ~1023u;
   const uint32_t b_base = base + (uint32_t)RA * kATileBytes;
   auto a_raw = [&](int s) { return base + (uint32_t)s * kATileBytes; };
@@ -660,43 +841,51 @@ gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       mbar_init(b_empty(s), 1);
     }
     for (int s = 0; s < TA; ++s) {
-      mbar_init(ready(s), 4);
+      mbar_init(ready(s), 4 * CG);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(acc_full(b), 1);
-      mbar_init(acc_empty(b), 4);  // one per epilogue warp
+      mbar_init(acc_empty(b), 4 * CG);  // one per epilogue warp (of both CTAs)
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     smem_u32(&tmem_base_s)),
-                 "r"((uint32_t)P.tmem_cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  if (warp == 1) {   // the same warp of both CTAs of a pair
+    if (CG == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                       smem_u32(&tmem_base_s)),
+                   "r"((uint32_t)P.tmem_cols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                       smem_u32(&tmem_base_s)),
+                   "r"((uint32_t)P.tmem_cols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();   // the peer's barriers are initialised before anything remote
+  else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_d = tmem_base_s;
   // every role walks the same sequence of k-steps: 128-row blocks b, b + grid, ...; all n-tiles
   // of a block back to back (the block's A tiles come from HBM once, then from L2)
-  const int my_blocks = P.m_tiles > (int)blockIdx.x
-                            ? (P.m_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int my_blocks = P.m_tiles > unit0 ? (P.m_tiles - unit0 + ustride - 1) / ustride : 0;
   const int n_tiles_cta = my_blocks * P.n_tiles;
-  const bool prof = (P.dbg & 16) && blockIdx.x == 0;
+  const bool prof = PROF && (P.dbg & 16) && blockIdx.x == 0;
   unsigned long long w0 = 0, w1 = 0, w2 = 0;
   const long long t_begin = clock64();
   unsigned long long t_begin_ns = 0;
-  if (P.dbg & 16) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_begin_ns));
+  if (PROF && (P.dbg & 16)) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_begin_ns));
 
   if (warp == 0) {
     // ===== raw A producer =====
     if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
       Ring ra{0, 0u};
-      for (int mb = blockIdx.x; mb < P.m_tiles; mb += gridDim.x) {
-        const int m0 = mb * kBM;
+      for (int mb = unit0; mb < P.m_tiles; mb += ustride) {
+        const int m0 = (mb * CG + (int)rank) * kBM;
         for (int kk = 0, kt = 0; kk < P.n_tiles * nk; ++kk, kt = kt + 1 == nk ? 0 : kt + 1, ra.next(RA)) {
           const int s = ra.s;
           mbar_wait_prof(a_empty(s), ra.ph ^ 1u, prof, w0);
@@ -719,23 +908,30 @@ gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapBl) : "memory");
       Ring rb{0, 0u};
       for (int tl = 0, nt = 0; tl < n_tiles_cta; ++tl, nt = nt + 1 == P.n_tiles ? 0 : nt + 1) {
-        const int n0 = nt * BN;
+        const int n0 = nt * BN + (int)rank * (BN / CG);   // this CTA's rows of the W tile
         for (int kt = 0; kt < nk; ++kt, rb.next(SB)) {
           const int s = rb.s;
           mbar_wait_prof(b_empty(s), rb.ph ^ 1u, prof, w0);
-          mbar_expect_tx(b_full(s), 2 * b_bytes);
-          tma_load_2d(b_hi(s), &mapBh, b_full(s), kt * kBK, n0);
-          tma_load_2d(b_lo(s), &mapBl, b_full(s), kt * kBK, n0);
+          if (CG == 2) {
+            const uint32_t lbar = mapa_u32(b_full(s), 0u);   // the leader's barrier counts both halves
+            if (leader) mbar_expect_tx(b_full(s), 2 * CG * b_bytes);
+            tma_load_2d_pair(b_hi(s), &mapBh, lbar, kt * kBK, n0);
+            tma_load_2d_pair(b_lo(s), &mapBl, lbar, kt * kBK, n0);
+          } else {
+            mbar_expect_tx(b_full(s), 2 * b_bytes);
+            tma_load_2d(b_hi(s), &mapBh, b_full(s), kt * kBK, n0);
+            tma_load_2d(b_lo(s), &mapBl, b_full(s), kt * kBK, n0);
+          }
         }
       }
       if (prof) { g_ts_prof[2] = w0; g_ts_prof[3] = (unsigned long long)(clock64() - t_begin); }
     }
   } else if (warp == 1) {
     // ===== MMA issuer: A from TMEM, W from shared memory.  The whole warp walks the loop
-    // (uniform control flow); one elected lane issues =====
-    {
+    // (uniform control flow); one elected lane issues.  CTA pairs: the leader only =====
+    if (leader) {
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
-                             ((uint32_t)(kBM >> 4) << 24);
+                             ((uint32_t)((CG * kBM) >> 4) << 24);
       Ring rb{0, 0u};
       for (int tl = 0; tl < n_tiles_cta; ++tl) {
         const int buf = tl & 1;
@@ -756,33 +952,51 @@ gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
             for (int k = 0; k < kBK / 8; ++k) {   // UMMA_K = 8 tf32: 8 TMEM columns / 32 bytes of W
               const uint32_t acc = (kt > 0 || k > 0) ? 1u : 0u;
-              mma_tf32_ts(dc, ah + 8u * k, dbh + 2u * k, idesc, acc);
-              if (P.dbg & 1) continue;
-              mma_tf32_ts(dcc, al + 8u * k, dbh + 2u * k, idesc, split_acc ? acc : 1u);
-              mma_tf32_ts(dcc, ah + 8u * k, dbl + 2u * k, idesc, 1u);
+              if (CG == 2) {
+                mma_tf32_ts_pair(dc, ah + 8u * k, dbh + 2u * k, idesc, acc);
+                mma_tf32_ts_pair(dcc, al + 8u * k, dbh + 2u * k, idesc, split_acc ? acc : 1u);
+                mma_tf32_ts_pair(dcc, ah + 8u * k, dbl + 2u * k, idesc, 1u);
+              } else {
+                mma_tf32_ts(dc, ah + 8u * k, dbh + 2u * k, idesc, acc);
+                if (P.dbg & 1) continue;
+                mma_tf32_ts(dcc, al + 8u * k, dbh + 2u * k, idesc, split_acc ? acc : 1u);
+                mma_tf32_ts(dcc, ah + 8u * k, dbl + 2u * k, idesc, 1u);
+              }
             }
-            tcgen05_commit(b_empty(sb));   // W stage and TMEM A stage (same ring position) are free
+            // W stage and TMEM A stage (same ring position) are free — in both CTAs of a pair
+            if (CG == 2) tcgen05_commit_pair(b_empty(sb));
+            else tcgen05_commit(b_empty(sb));
           }
           __syncwarp();
         }
-        if (elect_one()) tcgen05_commit(acc_full(buf));
+        if (elect_one()) {
+          if (CG == 2) tcgen05_commit_pair(acc_full(buf));
+          else tcgen05_commit(acc_full(buf));
+        }
         __syncwarp();
       }
       if (prof && lane == 0) {
         g_ts_prof[4] = w0; g_ts_prof[5] = w1; g_ts_prof[6] = w2;
         g_ts_prof[7] = (unsigned long long)(clock64() - t_begin);
-        g_ts_prof[14] = g_ts_prof[15] = 0;
       }
     }
-  } else if (warp < 6) {
-    // ===== splitter: warps 2..5, thread = tile row = TMEM lane (warp % 4 = lane quarter) =====
+  } else if (warp < 6 || warp >= 11) {
+    // ===== splitter: two groups of four warps (2..5 and 11..14) take alternate k-steps — one
+    // group's chain wait -> ld.shared -> cvt -> tcgen05.st -> wait::st -> arrive is ~1,000 clocks
+    // per step, twice what the MMAs of a CTA pair need.  Thread = tile row = TMEM lane
+    // (warp % 4 = lane quarter) =====
+    const int grp = warp < 6 ? 0 : 1;
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const uint32_t ta0 = tmem_d + ((uint32_t)(q * 32) << 16) + a_col0;
     const uint32_t sw = (uint32_t)(row & 7);
     const int n_steps = n_tiles_cta * nk;
     Ring ra{0, 0u}, rt{0, 0u};
-    for (int it = 0; it < n_steps; ++it, ra.next(RA), rt.next(TA)) {
+    if (grp) {
+      ra.next(RA);
+      rt.next(TA);
+    }
+    for (int it = grp; it < n_steps; it += 2, ra.next(RA), ra.next(RA), rt.next(TA), rt.next(TA)) {
       const int sa = ra.s, ta = rt.s;
       mbar_wait_prof(a_full(sa), ra.ph, prof, w0);
       const uint32_t src = a_raw(sa) + (uint32_t)row * 128u;
@@ -819,7 +1033,10 @@ gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       tmem_st_wait();
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(ready(ta));
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_cluster(mapa_u32(ready(ta), 0u));   // the leader issues the MMAs
+        else mbar_arrive(ready(ta));
+      }
     }
     if (prof && threadIdx.x == 64) {
       g_ts_prof[8] = w0; g_ts_prof[9] = w1;
@@ -828,24 +1045,38 @@ gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   } else {
     // ===== epilogue: warps 6..9 =====
     const int q = warp & 3;
-    const uint32_t epi = b_base + (uint32_t)SB * 2u * b_bytes + (uint32_t)(q * kEpiWarpBytes);
+    const uint32_t epi0 = b_base + (uint32_t)SB * 2u * b_bytes;   // 1024-byte aligned
+    const uint32_t epi = epi0 + (uint32_t)(q * kEpiWarpBytes);
+    const uint32_t stage = epi0 + (uint32_t)(q * kEpiTmaWarpBytes);
     const bool vec_ok = (P.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(P.C) & 15) == 0);
-    for (int tl = 0, nt = 0, mb = blockIdx.x; tl < n_tiles_cta; ++tl) {
+    int blk = 0;
+    EpiProf pf{prof && warp == 6, 0, 0, 0, 0};
+    if (P.tma_store && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&mapC) : "memory");
+    for (int tl = 0, nt = 0, mb = unit0; tl < n_tiles_cta; ++tl) {
       const int buf = tl & 1;
       mbar_wait_prof(acc_full(buf), (uint32_t)(tl >> 1) & 1u, prof, w0);
       tcgen05_fence_after();
       const uint32_t tbase = tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * acc_stride);
-      gemm_epilogue_rows<0>(P, tbase, BN, BN, split_acc, epi, mb * kBM + q * 32, nt * BN, lane,
-                            vec_ok);
+      if (P.tma_store)
+        gemm_epilogue_rows_tma(P, &mapC, tbase, BN, BN, split_acc, stage,
+                               (mb * CG + (int)rank) * kBM + q * 32, nt * BN, lane, blk,
+                               pf);
+      else
+        gemm_epilogue_rows<0>(P, tbase, BN, BN, split_acc, epi, (mb * CG + (int)rank) * kBM + q * 32,
+                              nt * BN, lane, vec_ok);
       if (++nt == P.n_tiles) {
         nt = 0;
-        mb += gridDim.x;
+        mb += ustride;
       }
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(acc_empty(buf));
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_cluster(mapa_u32(acc_empty(buf), 0u));
+        else mbar_arrive(acc_empty(buf));
+      }
     }
-    if ((P.dbg & 16) && threadIdx.x == 192 && blockIdx.x < 160) {
+    if (P.tma_store && elect_one()) tma_store_wait_all();   // shared memory is read, C is written
+    if (PROF && (P.dbg & 16) && threadIdx.x == 192 && blockIdx.x < 160) {
       unsigned long long ns;
       asm volatile("mov.u64 %0, %globaltimer;" : "=l"(ns));
       g_ts_cta[2 * blockIdx.x] = (unsigned long long)(clock64() - t_begin);
@@ -854,15 +1085,23 @@ gemm_ts_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (prof && threadIdx.x == 192) {
       g_ts_prof[11] = w0; g_ts_prof[12] = (unsigned long long)(clock64() - t_begin);
       g_ts_prof[13] = (unsigned long long)n_tiles_cta * (unsigned long long)nk;
+      g_ts_prof[14] = pf.a + (pf.b << 32);   // packed: the probe prints them split
+      g_ts_prof[15] = pf.c + (pf.d << 32);
     }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();   // the peer's shared memory and TMEM are in use until here
+  else __syncthreads();
   if (warp == 1) {
     tcgen05_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
-                 "r"((uint32_t)P.tmem_cols)
-                 : "memory");
+    if (CG == 2)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
+                   "r"((uint32_t)P.tmem_cols)
+                   : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d),
+                   "r"((uint32_t)P.tmem_cols)
+                   : "memory");
   }
 }
 
@@ -1312,6 +1551,7 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
   }
   GemmParams P;
   P.dbg = 0;
+  P.tma_store = 0;
   P.ts_ra = P.ts_sb = P.ts_ta = 0;
   P.bias = bias;
   P.relu = relu != 0;
@@ -1365,12 +1605,21 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
     if (const char* e = getenv("PYGB_GEMM_SPLIT_ACC")) P.split_acc = P.split_acc && atoi(e) != 0;
     const int acc_stride = P.BN * (P.split_acc ? 2 : 1);
     P.acc_bufs = 2;
-    P.m_tiles = (int)ceil_div(M, kBM);
+    // CTA pairs (cta_group::2) whenever there are at least two 256-row units; PYGB_GEMM_CG=1: single CTAs
+    int cg = M > 2 * kBM ? 2 : 1;
+    if (const char* e = getenv("PYGB_GEMM_CG")) cg = atoi(e) == 1 ? 1 : cg;
+    P.m_tiles = (int)ceil_div(M, cg * kBM);   // units of cg * 128 rows
     // ring depths: TMEM stages from what the accumulators leave; W stages (L2 latency) 3, or 4
     // when the tiles are small; every remaining 16 KB of shared memory is a raw A tile in flight
     const int nk = (int)ceil_div(K, kBK);
-    const size_t b_stage = 2 * (size_t)P.BN * kBK * 4;
-    const size_t budget = 226 * 1024 - 1024 - kEpiBytes;
+    const size_t b_stage = 2 * (size_t)(P.BN / cg) * kBK * 4;   // per CTA: its part of Wh and Wl
+    // C through TMA stores when it is an ordinary 16-byte aligned matrix (not routed)
+    // (N % 4: the store engine clips columns >= N in 16-byte units — measured: with N = 47 it
+    // wrote column 47 of a wider output matrix)
+    P.tma_store = (!route && C && aligned16(C) && ldc % 4 == 0 && N % 4 == 0) ? 1 : 0;
+    if (const char* e = getenv("PYGB_GEMM_TMA_STORE")) P.tma_store = P.tma_store && atoi(e) != 0;
+    const size_t epi_bytes = P.tma_store ? (size_t)kEpiTmaBytes : (size_t)kEpiBytes;
+    const size_t budget = 226 * 1024 - 1024 - epi_bytes;
     int ta = (512 - 2 * acc_stride) / kTsACols;
     int sb = 4;
     if (const char* e = getenv("PYGB_GEMM_TS_SB")) sb = atoi(e);
@@ -1392,21 +1641,49 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
     int tc = 32;
     while (tc < 2 * acc_stride + ta * kTsACols) tc <<= 1;
     P.tmem_cols = tc;
-    const size_t smem = ra * (size_t)kATileBytes + sb * b_stage + kEpiBytes + 1024;
+    const size_t smem = ra * (size_t)kATileBytes + sb * b_stage + epi_bytes + 1024;
     (void)nk;
-    CUtensorMap mapA, mapBh, mapBl;
+    CUtensorMap mapA, mapBh, mapBl, mapC;
     int rc = a_slices > 1 ? make_map_a(&mapA, A, M, a_kw, lda, a_slices, a_plane, kBM, kBK)
                           : make_map(&mapA, A, M, K, lda, kBM, kBK);
     if (rc) return rc;
-    rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN, kBK);
+    rc = make_map(&mapBh, Wh, Np, Kp, Kp, P.BN / cg, kBK);
     if (rc) return rc;
-    rc = make_map(&mapBl, Wl, Np, Kp, Kp, P.BN, kBK);
+    rc = make_map(&mapBl, Wl, Np, Kp, Kp, P.BN / cg, kBK);
     if (rc) return rc;
-    int64_t ctas = P.m_tiles < sms ? P.m_tiles : sms;
-    if (route && route->max_ctas > 0 && ctas > route->max_ctas) ctas = route->max_ctas;
-    PYGB_CUDA(cudaFuncSetAttribute(gemm_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)(226 * 1024)));
-    gemm_ts_kernel<<<(unsigned)ctas, kTsThreads, smem, st>>>(mapA, mapBh, mapBl, P);
+    if (P.tma_store) {
+      rc = make_map(&mapC, C, M, N, ldc, 32, 32);   // 32 x 32 fp32 blocks, 128-byte swizzle
+      if (rc) return rc;
+    } else {
+      mapC = mapA;   // unused
+    }
+    int64_t units = P.m_tiles < sms / cg ? P.m_tiles : sms / cg;
+    if (route && route->max_ctas > 0 && units * cg > route->max_ctas)
+      units = route->max_ctas / cg > 0 ? route->max_ctas / cg : 1;
+    const int64_t ctas = units * cg;
+    if (cg == 2) {
+      auto kern = (P.dbg & 16) ? gemm_ts_kernel<2, true> : gemm_ts_kernel<2, false>;
+      PYGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(226 * 1024)));
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)ctas);
+      cfg.blockDim = dim3(kTsThreads);
+      cfg.dynamicSmemBytes = smem;
+      cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      PYGB_CUDA(cudaLaunchKernelEx(&cfg, kern, mapA, mapBh, mapBl, mapC, P));
+    } else {
+      auto kern = (P.dbg & 16) ? gemm_ts_kernel<1, true> : gemm_ts_kernel<1, false>;
+      PYGB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(226 * 1024)));
+      kern<<<(unsigned)ctas, kTsThreads, smem, st>>>(mapA, mapBh, mapBl, mapC, P);
+    }
     PYGB_LAUNCH_CHECK();
     if (P.dbg & 16) {   // probe: synchronises and prints CTA 0's wait clocks
       unsigned long long h[16], hc[2 * 160];
@@ -1425,11 +1702,12 @@ static int gemm_xw_impl(const float* A, int64_t lda, int64_t a_slices, int64_t a
                 cmin, cmax, nmin, nmax, hc[0], hc[1]);
       }
       fprintf(stderr,
-              "[ts prof] M=%d K=%d N=%d BN=%d ra=%d sb=%d ta=%d steps=%llu | A-prod wait a_empty %llu of %llu"
+              "[ts prof] cg=%d M=%d K=%d N=%d BN=%d ra=%d sb=%d ta=%d steps=%llu | A-prod wait a_empty %llu of %llu"
               " | W-prod wait b_empty %llu of %llu | MMA wait acc_empty %llu b_full %llu ready %llu of"
-              " %llu (mma issue %llu, commits %llu) | split wait a_full %llu b_empty %llu of %llu | epi wait acc_full %llu of %llu\n",
-              P.M, P.K, P.N, P.BN, ra, sb, ta, h[13], h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7],
-              h[14], h[15], h[8], h[9], h[10], h[11], h[12]);
+              " %llu (epi: tmem ld %llu, stage wait %llu, st.shared+fence %llu, issue %llu) | split wait a_full %llu b_empty %llu of %llu | epi wait acc_full %llu of %llu\n",
+              cg, P.M, P.K, P.N, P.BN, ra, sb, ta, h[13], h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7],
+              h[14] & 0xffffffffull, h[14] >> 32, h[15] & 0xffffffffull, h[15] >> 32, h[8], h[9],
+              h[10], h[11], h[12]);
     }
     return PYGB_OK;
   }
@@ -1588,6 +1866,7 @@ int pygb_gemm_xw_bf16(const void* A, int64_t lda, int64_t M, int64_t K, const vo
   }
   GemmParams P;
   P.dbg = 0;
+  P.tma_store = 0;
   P.ts_ra = P.ts_sb = P.ts_ta = 0;
   P.bias = bias;
   P.relu = relu != 0;

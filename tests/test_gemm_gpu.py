@@ -133,6 +133,34 @@ def test_gemm_tile_256_sliced_and_routed(dev, monkeypatch):
         assert torch.equal(o[2:], ref[:, q * Fc:(q + 1) * Fc]) and float(o[:2].max()) == -7.0
 
 
+@pytest.mark.parametrize('M', [900, 130])
+def test_gemm_default_kernel_sliced_and_routed(dev, monkeypatch, M):
+    """The default 3-pass kernel (A in tensor memory; CTA pairs when M > 256) with a slice-major
+    A and a routed epilogue (the multi-GPU transform's local case) == the plain call, bit for bit;
+    and the TMA-store epilogue == the transposing one."""
+    from torch_geometric import ops
+    g = torch.Generator().manual_seed(6)
+    S, Kc, N, Fc = 4, 32, 256, 64
+    x = torch.randn(M, S * Kc, generator=g).to(dev)
+    w = (torch.randn(S * Kc, N, generator=g) / (S * Kc) ** 0.5).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    ref = ops.gemm_xw_raw(x, w, b, relu=True)
+    monkeypatch.setenv('PYGB_GEMM_TMA_STORE', '0')
+    assert torch.equal(ops.gemm_xw_raw(x, w, b, relu=True), ref)
+    monkeypatch.delenv('PYGB_GEMM_TMA_STORE')
+    monkeypatch.setenv('PYGB_GEMM_CG', '1')
+    assert torch.equal(ops.gemm_xw_raw(x, w, b, relu=True), ref)
+    monkeypatch.delenv('PYGB_GEMM_CG')
+    planes = torch.zeros((S, M + 11, Kc), device=dev)
+    planes[:, :M] = x.view(M, S, Kc).permute(1, 0, 2)
+    assert torch.equal(ops.gemm_xw_raw(planes, w, b, relu=True, rows=M), ref)
+    outs = [torch.full((M + 2, Fc), -7.0, device=dev) for _ in range(N // Fc)]
+    tab = torch.tensor([o.data_ptr() for o in outs], dtype=torch.int64).to(dev)
+    ops.gemm_xw_routed_raw(x, w, b, Fc, tab, 2, Fc, relu=True)
+    for q, o in enumerate(outs):
+        assert torch.equal(o[2:], ref[:, q * Fc:(q + 1) * Fc]) and float(o[:2].max()) == -7.0
+
+
 @pytest.mark.parametrize('M,K,N', SHAPES[:5])
 def test_gemm_tf32_single_pass(dev, M, K, N):
     from torch_geometric import ops
