@@ -14,6 +14,17 @@
 // consumes the stage.  The layer is HBM-bound (M = 2.4M rows, K,N <= 256), so the two
 // extra MMAs hide under the memory time.
 //
+// Kernels in this file:
+//   gemm_ts_kernel<CG, PROF>  the default 3-pass kernel: A_hi / A_lo live in TENSOR memory
+//                             (tcgen05.st by the splitter warps, `[a_tmem], b_desc` MMAs), CTA
+//                             pairs (cta_group::2, CG = 2) whenever M > 256, TMA-store epilogue
+//                             for plain outputs; see the comment block above it
+//   gemm_tf32_kernel<...>     operands in shared memory: 1-pass TF32, bf16 (kind::f16), the
+//                             PYGB_GEMM_TILE shapes, and PYGB_GEMM_TS=0
+//   gemm_xtg_kernel<...>      K5t, dW = X^T G
+// All of them issue tcgen05.mma from ONE lane picked by elect.sync inside a warp that walks the
+// loop in uniform control flow (see elect_one()).  What follows describes gemm_tf32_kernel.
+//
 // Persistent CTAs (one per SM) of 10 warps: warp 0 TMA producer, warp 1 TMEM
 // allocator + MMA issuer (one elected lane), warps 2-5 splitter, warps 6-9 epilogue
 // (TMEM -> registers -> global).  Tile 128 x BN (BN = N rounded to 16, <= 256) x 32
