@@ -740,7 +740,7 @@ def run_b200(args):
 
     # ---- roofline of the dominant kernel: K1 at F = hidden ---------------------
     K1_NAMES = ('pygb_seg_gather_reduce', 'pygb_seg_gather_reduce_stream',
-                'pygb_seg_gather_reduce_stream_routed')
+                'pygb_seg_gather_reduce_stream_hinted', 'pygb_seg_gather_reduce_stream_routed')
     k1_width = graph.plan.widths(hid, itemsize)[1] if sliced else hid
     k1 = [(e0.elapsed_time(e1), a) for (name, a, e0, e1) in log
           if name in K1_NAMES and a[4] == k1_width]
@@ -1025,7 +1025,7 @@ def run_config(args):
     # ---- roofline of the dominant aggregation kernel (SURVEY §8d bytes) --------
     peak, peak_src = peaks()
     if name == 'pubmed_pruning':
-        kname, width = ('pygb_seg_gather_reduce_stream',), 500
+        kname, width = ('pygb_seg_gather_reduce_stream', 'pygb_seg_gather_reduce_stream_hinted'), 500
         sel = [(e0.elapsed_time(e1)) for (nm, a_, e0, e1) in log if nm in kname and a_[4] == width]
         kbytes = k1_bytes(e_prime, n, width, itemsize)
         ktext = 'K1 seg_stream_kernel + fixup, F=500 (layer 1 aggregates first: (A X) W)'

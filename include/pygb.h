@@ -174,6 +174,23 @@ int pygb_seg_gather_reduce_stream(int reduce, int dtype, const void* x, int64_t 
                                   int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
                                   void* ws, size_t ws_bytes, pygb_stream_t s);
 
+/* L2 residency hints for the gather (no counterpart in the reference; the aggregation is HBM-bound
+ * and on a power-law graph a few percent of the source rows take a third of the gathers).
+ * pygb_seg_mark_hot sets bit 30 of every slot of a flagged index stream whose source row is
+ * gathered at least `threshold` times (freq[j] = number of slots that name source j; ids must fit
+ * 30 bits); pygb_seg_gather_reduce_stream_hinted is pygb_seg_gather_reduce_stream for such a stream:
+ * marked gathers carry an L2 evict_last policy, the others evict_normal.  Results are bit-identical
+ * to the unhinted call. */
+int pygb_seg_mark_hot(int32_t* idx_flagged, int64_t E, const int32_t* freq, int64_t n_src,
+                      int32_t threshold, pygb_stream_t s);
+int pygb_seg_gather_reduce_stream_hinted(int reduce, int dtype, const void* x, int64_t ldx,
+                                         int64_t F, const int32_t* rowptr,
+                                         const int32_t* idx_flagged, const float* edge_w,
+                                         const float* bias, int64_t n_rows, int64_t E,
+                                         const int32_t* nz_rows, const int32_t* sub_info,
+                                         int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
+                                         void* ws, size_t ws_bytes, pygb_stream_t s);
+
 /* pygb_seg_gather_reduce_stream WITHOUT a workspace argument and without any device
  * allocation (no counterpart in the reference: added
  * for callers that cannot call cudaMalloc — code under CUDA graph capture,

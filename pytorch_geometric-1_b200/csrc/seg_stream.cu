@@ -70,6 +70,8 @@ struct StreamParams {
   int max_ctas;        // > 0: cap of the persistent grid; < 0: leave |max_ctas| SMs to a
                        // concurrent kernel (grid = (SMs + max_ctas) x resident CTAs per SM)
   int64_t out_off;  // bytes
+  int hot;          // the index stream carries a "hot source row" hint in bit 30 (pygb_seg_mark_hot):
+                    // those gathers ask L2 to keep the line (evict_last)
 };
 
 template <typename T>
@@ -108,6 +110,11 @@ seg_stream_kernel(const StreamParams P) {
   const char* xb = static_cast<const char*>(P.x) + fl * 16;
   asm volatile("" : "+l"(xb));  // keep the per-lane base in registers
   const uint32_t ldxb = (uint32_t)(P.ldx * sizeof(T));
+  // L2 eviction priority of the gathered rows: rows of frequently gathered sources (bit 30 of the
+  // index stream, when the caller marked them) are kept in preference to the rest
+  const int hot_bit = P.hot ? 0x40000000 : 0;
+  const int idx_mask = P.hot ? 0x3fffffff : 0x7fffffff;
+  const uint64_t pol_hot = l2_policy_evict_last(), pol_norm = l2_policy_evict_normal();
   const int* __restrict__ idxf = P.idxf;
   const float* __restrict__ ew = P.ew;
   const int* __restrict__ nz_rows = P.nz_rows;
@@ -188,7 +195,7 @@ seg_stream_kernel(const StreamParams P) {
 #pragma unroll
         for (int g = 0; g < G; ++g) {
           craw[g] = __shfl_sync(kFull, idx_cur, lane0 + g);
-          src[g] = xb + (uint64_t)(uint32_t)(craw[g] & 0x7fffffff) * ldxb;
+          src[g] = xb + (uint64_t)(uint32_t)(craw[g] & idx_mask) * ldxb;
         }
 #pragma unroll
         for (int g = 0; g < G; ++g) {
@@ -196,7 +203,8 @@ seg_stream_kernel(const StreamParams P) {
 #pragma unroll
             for (int v = 0; v < VPL; ++v)
               if (act[v])
-                cp_async16(sb + (uint32_t)(g * C::DATA_B + v * 512), src[g] + v * LPF * 16);
+                cp_async16_hint(sb + (uint32_t)(g * C::DATA_B + v * 512), src[g] + v * LPF * 16,
+                                (craw[g] & hot_bit) ? pol_hot : pol_norm);
           }
         }
         if (lead) {
@@ -354,6 +362,15 @@ flag_idx_kernel(const int* __restrict__ rowptr, int64_t n_rows, int* __restrict_
        r += (int64_t)gridDim.x * 256) {
     const int e = rowptr[r + 1];
     if (e > rowptr[r]) idxf[e - 1] |= (int)0x80000000;
+  }
+}
+
+// bit 30 on every slot whose source row is gathered at least `threshold` times
+__global__ void __launch_bounds__(256)
+mark_hot_kernel(int* __restrict__ idxf, int64_t E, const int* __restrict__ freq, int threshold) {
+  for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < E; e += (int64_t)gridDim.x * 256) {
+    const int v = idxf[e];
+    if (__ldg(freq + (v & 0x3fffffff)) >= threshold) idxf[e] = v | 0x40000000;
   }
 }
 
@@ -522,7 +539,8 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
                            const float* bias, int64_t n_rows, int64_t E, const int32_t* nz_rows,
                            const int32_t* sub_info, int32_t Ts, int64_t n_sub, void* out,
                            void* const* out_tab, int64_t blk_rows, int64_t sub_rot, int64_t ldo,
-                           int64_t max_ctas, void* ws, size_t ws_bytes, pygb_stream_t s) {
+                           int64_t max_ctas, void* ws, size_t ws_bytes, pygb_stream_t s,
+                           int hot = 0) {
   PYGB_REQUIRE(reduce == PYGB_SUM || reduce == PYGB_MEAN,
                "pygb_seg_gather_reduce_stream: bad reduce %d", reduce);
   PYGB_REQUIRE(dtype == PYGB_F32 || dtype == PYGB_BF16,
@@ -576,6 +594,7 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
     P.sub_rot = (int)sub_rot;
     P.max_ctas = (int)(max_ctas > -(1 << 20) && max_ctas < (1 << 30) ? max_ctas : 0);
     P.out_off = f0 * esz;
+    P.hot = hot;
     P.ldo = ldo;
     P.sub_info = sub_info;
     P.nz_rows = nz_rows;
@@ -616,6 +635,31 @@ int pygb_seg_gather_reduce_stream_routed(int reduce, int dtype, const void* x, i
   return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
                          nz_rows, sub_info, Ts, n_sub, nullptr, out_tab, blk_rows, sub_rot, ldo,
                          max_ctas, ws, ws_bytes, s);
+}
+
+// pygb_seg_gather_reduce_stream with an index stream that carries pygb_seg_mark_hot's hints
+int pygb_seg_gather_reduce_stream_hinted(int reduce, int dtype, const void* x, int64_t ldx,
+                                         int64_t F, const int32_t* rowptr,
+                                         const int32_t* idx_flagged, const float* edge_w,
+                                         const float* bias, int64_t n_rows, int64_t E,
+                                         const int32_t* nz_rows, const int32_t* sub_info,
+                                         int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
+                                         void* ws, size_t ws_bytes, pygb_stream_t s) {
+  PYGB_REQUIRE(out || n_rows == 0 || F == 0, "pygb_seg_gather_reduce_stream_hinted: null pointer");
+  return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
+                         nz_rows, sub_info, Ts, n_sub, out, nullptr, 0, 0, ldo, 0, ws, ws_bytes, s,
+                         1);
+}
+
+int pygb_seg_mark_hot(int32_t* idx_flagged, int64_t E, const int32_t* freq, int64_t n_src,
+                      int32_t threshold, pygb_stream_t s) {
+  PYGB_REQUIRE(E >= 0 && E < (1ll << 31) && n_src >= 0 && n_src <= (1ll << 30),
+               "pygb_seg_mark_hot: bad sizes (source ids must fit 30 bits)");
+  if (E == 0) return PYGB_OK;
+  PYGB_REQUIRE(idx_flagged && freq, "pygb_seg_mark_hot: null pointer");
+  mark_hot_kernel<<<grid1d(E), 256, 0, as_stream(s)>>>(idx_flagged, E, freq, threshold);
+  PYGB_LAUNCH_CHECK();
+  return PYGB_OK;
 }
 
 }  // extern "C"

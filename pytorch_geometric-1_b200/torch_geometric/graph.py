@@ -77,6 +77,28 @@ class CSR(object):
         self._items[key] = out
         return out
 
+    def flagged_hot(self, n_hot):
+        """``flagged('col')`` with bit 30 set on the slots of the ``n_hot`` most frequently
+        gathered source rows (pygb_seg_mark_hot): the index stream of
+        pygb_seg_gather_reduce_stream_hinted, whose gathers ask L2 to keep those rows.  Built once
+        per (graph, n_hot); ``None`` when every source is gathered equally often or ids need
+        more than 30 bits."""
+        key = ('hot', int(n_hot))
+        if key in self._items:
+            return self._items[key]
+        out = None
+        n_src = int(self.col.max().item()) + 1 if self.E > 0 else 0
+        if 0 < n_hot < n_src <= (1 << 30):
+            freq = torch.bincount(self.col, minlength=n_src)
+            thr = int(torch.topk(freq, int(n_hot), sorted=True).values[-1].item())
+            if thr > int(freq.min().item()):
+                out = self.flagged('col').clone()
+                freq32 = freq.to(torch.int32)
+                nat.call('pygb_seg_mark_hot', out.device, nat.ptr(out), self.E, nat.ptr(freq32), n_src,
+                         thr)
+        self._items[key] = out
+        return out
+
     @property
     def device(self):
         return self.rowptr.device

@@ -17,6 +17,11 @@ NEG_INF = float('-inf')
 # padded, else the one-warp-per-row kernel.  STREAM_T forces the item size (tests).
 STREAM = True
 STREAM_T = None
+# K1: megabytes of L2 the most frequently gathered source rows may claim (evict_last hints on
+# their gathers, pygb_seg_mark_hot); 0 disables the hints
+# (products graph, tools/k1_hot_probe.py: F=256 9.3-9.4 -> 8.9-9.05 ms, F=100 -3..5 %, F=64 -7 %
+# with 16-32 MB; larger budgets lose again)
+K1_HOT_MB = int(os.environ.get('PYGB_K1_HOT_MB', '24'))
 LINE_ALIGN = os.environ.get('PYGB_LINE_ALIGN', '1') not in ('', '0')
 
 
@@ -144,9 +149,15 @@ def seg_gather_reduce_raw(x, csr, idx, reduce='sum', w=None, wperm=None, bias=No
         else:
             raise ValueError('seg_gather_reduce_raw: idx must be csr.col or csr.perm '
                              '(or come with an idx_key)')
+        entry = 'pygb_seg_gather_reduce_stream'
+        if idx is csr.col and K1_HOT_MB > 0 and x2.size(0) * ldx * x2.element_size() > (K1_HOT_MB << 21):
+            # source rows far beyond L2: ask it to keep the most frequently gathered ones
+            hot = csr.flagged_hot((K1_HOT_MB << 20) // (ldx * x2.element_size()))
+            if hot is not None:
+                idxf, entry = hot, 'pygb_seg_gather_reduce_stream_hinted'
         ws_bytes = nat.workspace('pygb_seg_stream_workspace', dt, n_sub, F)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        nat.call('pygb_seg_gather_reduce_stream', dev, nat.MEAN if reduce == 'mean' else nat.SUM,
+        nat.call(entry, dev, nat.MEAN if reduce == 'mean' else nat.SUM,
                  dt, nat.ptr(x2), ldx, F, nat.ptr(csr.rowptr), nat.ptr(idxf), nat.ptr(w),
                  nat.ptr(bias), csr.n_rows, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub,
                  nat.ptr(out), ldo, nat.ptr(ws), ws_bytes)

@@ -218,3 +218,40 @@ def test_gat_fork_shapes_run_on_streaming_kernels(dev, H, C, concat, bwd_stream)
     assert_close(conv.weight.grad, ref.weight.grad, 2e-4, 'dW')
     assert_close(conv.att.grad, ref.att.grad, 2e-4, 'datt')
     assert_close(conv.bias.grad, ref.bias.grad, 2e-4, 'dbias')
+
+
+def test_k1_hot_row_hints_are_bit_identical(dev):
+    """pygb_seg_mark_hot sets bit 30 exactly on the slots of the most frequently gathered source
+    rows and leaves the row-end flags alone; pygb_seg_gather_reduce_stream_hinted (L2 evict_last
+    on those gathers) returns the bits of pygb_seg_gather_reduce_stream."""
+    from torch_geometric import _native as nat
+    from torch_geometric import ops
+    from torch_geometric.graph import Adj
+    n, E, F = 3000, 60000, 64
+    ei = skewed_graph(n, E, 21)
+    ei = torch.stack([ei[1], ei[0]])            # hub SOURCES: a few rows are gathered thousands of times
+    csr = Adj(ei.to(dev), 1, (n, n)).dst
+    base = csr.flagged('col')
+    hot = csr.flagged_hot(40)
+    assert hot is not None and hot is csr.flagged_hot(40)
+    col = csr.col.long()
+    freq = torch.bincount(col, minlength=n)
+    thr = torch.topk(freq, 40).values[-1]
+    want = freq[col] >= thr
+    assert torch.equal(((hot >> 30) & 1).bool(), want) and 0 < int(want.sum()) < E
+    assert torch.equal(hot & ~(1 << 30), base)
+    assert csr.flagged_hot(n + 5) is None       # everything "hot": no hint
+    x = _feat(n, F, 3).to(dev)
+    w = torch.rand(E, device=dev) + 0.5
+    Ts, n_sub, nz_rows, sub_info = csr.items(ops.STREAM_T)
+    ws_bytes = nat.workspace('pygb_seg_stream_workspace', nat.F32, n_sub, F)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    outs = []
+    for entry, idxf in (('pygb_seg_gather_reduce_stream', base),
+                        ('pygb_seg_gather_reduce_stream_hinted', hot)):
+        out = torch.full((n, F), float('nan'), device=dev)
+        nat.call(entry, dev, nat.SUM, nat.F32, nat.ptr(x), F, F, nat.ptr(csr.rowptr), nat.ptr(idxf),
+                 nat.ptr(w), None, n, E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub, nat.ptr(out),
+                 F, nat.ptr(ws), ws_bytes)
+        outs.append(out)
+    assert torch.equal(outs[0], outs[1]) and not torch.isnan(outs[0]).any()
