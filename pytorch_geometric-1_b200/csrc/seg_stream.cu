@@ -114,7 +114,8 @@ seg_stream_kernel(const StreamParams P) {
   // index stream, when the caller marked them) are kept in preference to the rest
   const int hot_bit = P.hot ? 0x40000000 : 0;
   const int idx_mask = P.hot ? 0x3fffffff : 0x7fffffff;
-  const uint64_t pol_hot = l2_policy_evict_last(), pol_norm = l2_policy_evict_normal();
+  const uint64_t pol_hot = l2_policy_evict_last();
+  const uint64_t pol_norm = P.hot == 2 ? l2_policy_evict_first() : l2_policy_evict_normal();
   const int* __restrict__ idxf = P.idxf;
   const float* __restrict__ ew = P.ew;
   const int* __restrict__ nz_rows = P.nz_rows;
@@ -595,6 +596,10 @@ static int seg_stream_impl(int reduce, int dtype, const void* x, int64_t ldx, in
     P.max_ctas = (int)(max_ctas > -(1 << 20) && max_ctas < (1 << 30) ? max_ctas : 0);
     P.out_off = f0 * esz;
     P.hot = hot;
+    if (hot) {
+      const char* e = getenv("PYGB_K1_COLD_FIRST");   // probe: unmarked gathers evict_first
+      if (e && atoi(e) != 0) P.hot = 2;
+    }
     P.ldo = ldo;
     P.sub_info = sub_info;
     P.nz_rows = nz_rows;
