@@ -740,7 +740,8 @@ def run_b200(args):
 
     # ---- roofline of the dominant kernel: K1 at F = hidden ---------------------
     K1_NAMES = ('pygb_seg_gather_reduce', 'pygb_seg_gather_reduce_stream',
-                'pygb_seg_gather_reduce_stream_hinted', 'pygb_seg_gather_reduce_stream_routed')
+                'pygb_seg_gather_reduce_stream_hinted', 'pygb_seg_gather_reduce_stream_routed',
+                'pygb_seg_gather_reduce_stream_routed_hinted')
     k1_width = graph.plan.widths(hid, itemsize)[1] if sliced else hid
     k1 = [(e0.elapsed_time(e1), a) for (name, a, e0, e1) in log
           if name in K1_NAMES and a[4] == k1_width]

@@ -191,6 +191,17 @@ int pygb_seg_gather_reduce_stream_hinted(int reduce, int dtype, const void* x, i
                                          int32_t Ts, int64_t n_sub, void* out, int64_t ldo,
                                          void* ws, size_t ws_bytes, pygb_stream_t s);
 
+/* pygb_seg_gather_reduce_stream_routed (below) for a stream marked by pygb_seg_mark_hot. */
+int pygb_seg_gather_reduce_stream_routed_hinted(int reduce, int dtype, const void* x, int64_t ldx,
+                                                int64_t F, const int32_t* rowptr,
+                                                const int32_t* idx_flagged, const float* edge_w,
+                                                const float* bias, int64_t n_rows, int64_t E,
+                                                const int32_t* nz_rows, const int32_t* sub_info,
+                                                int32_t Ts, int64_t n_sub, void* const* out_tab,
+                                                int64_t blk_rows, int64_t sub_rot, int64_t ldo,
+                                                int64_t max_ctas, void* ws, size_t ws_bytes,
+                                                pygb_stream_t s);
+
 /* pygb_seg_gather_reduce_stream WITHOUT a workspace argument and without any device
  * allocation (no counterpart in the reference: added
  * for callers that cannot call cudaMalloc — code under CUDA graph capture,

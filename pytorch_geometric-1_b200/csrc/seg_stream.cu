@@ -656,6 +656,23 @@ int pygb_seg_gather_reduce_stream_hinted(int reduce, int dtype, const void* x, i
                          1);
 }
 
+// pygb_seg_gather_reduce_stream_routed with an index stream that carries the hints
+int pygb_seg_gather_reduce_stream_routed_hinted(int reduce, int dtype, const void* x, int64_t ldx,
+                                                int64_t F, const int32_t* rowptr,
+                                                const int32_t* idx_flagged, const float* edge_w,
+                                                const float* bias, int64_t n_rows, int64_t E,
+                                                const int32_t* nz_rows, const int32_t* sub_info,
+                                                int32_t Ts, int64_t n_sub, void* const* out_tab,
+                                                int64_t blk_rows, int64_t sub_rot, int64_t ldo,
+                                                int64_t max_ctas, void* ws, size_t ws_bytes,
+                                                pygb_stream_t s) {
+  PYGB_REQUIRE(out_tab || n_rows == 0 || F == 0,
+               "pygb_seg_gather_reduce_stream_routed_hinted: null pointer table");
+  return seg_stream_impl(reduce, dtype, x, ldx, F, rowptr, idx_flagged, edge_w, bias, n_rows, E,
+                         nz_rows, sub_info, Ts, n_sub, nullptr, out_tab, blk_rows, sub_rot, ldo,
+                         max_ctas, ws, ws_bytes, s, 1);
+}
+
 int pygb_seg_mark_hot(int32_t* idx_flagged, int64_t E, const int32_t* freq, int64_t n_src,
                       int32_t threshold, pygb_stream_t s) {
   PYGB_REQUIRE(E >= 0 && E < (1ll << 31) && n_src >= 0 && n_src <= (1ll << 30),

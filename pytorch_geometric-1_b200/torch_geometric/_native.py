@@ -47,6 +47,9 @@ SIGNATURES = {
     'pygb_seg_mark_hot': (_I, [_P, _L, _P, _L, _I, _P]),
     'pygb_seg_gather_reduce_stream_hinted': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P,
                                                   _I, _L, _P, _L, _P, _Z, _P]),
+    'pygb_seg_gather_reduce_stream_routed_hinted': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L,
+                                                         _P, _P, _I, _L, _P, _L, _L, _L, _L, _P, _Z,
+                                                         _P]),
     'pygb_seg_gather_reduce_stream_static': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P,
                                                   _P, _I, _L, _P, _L, _P]),
     'pygb_seg_gather_reduce_stream_routed': (_I, [_I, _I, _P, _L, _L, _P, _P, _P, _P, _L, _L, _P, _P,

@@ -208,9 +208,15 @@ def seg_gather_reduce_routed_raw(x, csr, w_csr, bias, out_tab, blk_rows, ldo, re
             slot = int(csr.rowptr[min(int(start_row), csr.n_rows)].item())   # once per CSR
             csr._items[key] = slot
         sub_rot = min(slot // Ts, n_sub)
+    entry = 'pygb_seg_gather_reduce_stream_routed'
+    row_bytes = _ld(x2) * x2.element_size()
+    if K1_HOT_MB > 0 and x2.size(0) * row_bytes > (K1_HOT_MB << 21):
+        hot = csr.flagged_hot((K1_HOT_MB << 20) // row_bytes)     # see seg_gather_reduce_raw
+        if hot is not None:
+            idxf, entry = hot, 'pygb_seg_gather_reduce_stream_routed_hinted'
     ws_bytes = nat.workspace('pygb_seg_stream_workspace', dt, n_sub, F)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    nat.call('pygb_seg_gather_reduce_stream_routed', dev,
+    nat.call(entry, dev,
              nat.MEAN if reduce == 'mean' else nat.SUM, dt, nat.ptr(x2), _ld(x2), F,
              nat.ptr(csr.rowptr), nat.ptr(idxf), nat.ptr(_f32(w_csr)), nat.ptr(_f32(bias)),
              csr.n_rows, csr.E, nat.ptr(nz_rows), nat.ptr(sub_info), Ts, n_sub, nat.ptr(out_tab),
