@@ -144,3 +144,129 @@ def test_scatter_oracle_equals_aten_reductions():
         m = index == r
         if m.any():
             assert torch.allclose(sm[m], torch.softmax(logits[m], dim=0), rtol=1e-12, atol=1e-14)
+
+
+# ---- the widened rows (oracle/ref_next.py) -------------------------------------------------
+def _dense(ei, n, w=None):
+    """A[src, dst] with duplicate edges added up."""
+    A = torch.zeros(n, n, dtype=F64)
+    A.index_put_((ei[0], ei[1]), torch.ones(ei.size(1), dtype=F64) if w is None else w, accumulate=True)
+    return A
+
+
+def _digraph(n, E, seed, loops=False):
+    g = torch.Generator().manual_seed(seed)
+    src = torch.randint(0, n, (E,), generator=g)
+    dst = torch.randint(0, n, (E,), generator=g)
+    if not loops:
+        keep = src != dst
+        src, dst = src[keep], dst[keep]
+    return torch.stack([src, dst])
+
+
+def test_sgc_appnp_cheb_oracles_are_their_matrix_recurrences():
+    from oracle import ref_next as R
+    n, fin, fout = 30, 5, 4
+    ei = _digraph(n, 200, 7)
+    g = torch.Generator().manual_seed(8)
+    x = torch.randn(n, fin, generator=g, dtype=F64)
+    A_hat = _dense(ei, n) + torch.eye(n, dtype=F64)
+    s = A_hat.sum(1).pow(-0.5)
+    S = (s.view(-1, 1) * A_hat * s.view(1, -1)).t()          # propagation matrix: out = S x
+    # SGC (Wu et al. 2019): S^K X Theta
+    sg = R.SGConv(fin, fout, K=3).double()
+    want = torch.linalg.matrix_power(S, 3) @ x @ sg.lin.weight.detach().t() + sg.lin.bias.detach()
+    assert torch.allclose(sg(x, ei).detach(), want, rtol=1e-12, atol=1e-12)
+    # APPNP (Klicpera et al. 2019): Z^(k+1) = (1 - alpha) S Z^(k) + alpha H
+    z = x
+    for _ in range(4):
+        z = 0.85 * (S @ z) + 0.15 * x
+    assert torch.allclose(R.APPNP(4, 0.15)(x, ei), z, rtol=1e-12, atol=1e-12)
+    # ChebNet (Defferrard et al. 2016) with lambda_max = 2: L~ = -D^-1/2 A D^-1/2
+    A = _dense(ei, n)
+    d = A.sum(1).pow(-0.5)
+    d[torch.isinf(d)] = 0
+    L = -(d.view(-1, 1) * A * d.view(1, -1)).t()
+    ch = R.ChebConv(fin, fout, K=4).double()
+    with torch.no_grad():
+        ch.weight.normal_(generator=g)
+        ch.bias.uniform_(-1, 1, generator=g)
+    T = [x, L @ x]
+    for _ in range(2, 4):
+        T.append(2 * L @ T[-1] - T[-2])
+    want = sum(t @ ch.weight[k].detach() for k, t in enumerate(T)) + ch.bias.detach()
+    assert torch.allclose(ch(x, ei).detach(), want, rtol=1e-12, atol=1e-12)
+
+
+def test_sage_gin_graphconv_agnn_oracles_are_their_formulas():
+    from oracle import ref_next as R
+    n, fin, fout = 24, 5, 3
+    ei = _digraph(n, 150, 9, loops=True)
+    nl = ei[:, ei[0] != ei[1]]
+    g = torch.Generator().manual_seed(10)
+    x = torch.randn(n, fin, generator=g, dtype=F64)
+    A = _dense(nl, n)                                         # without the input's self-loops
+    # GraphSAGE-mean (Hamilton et al. 2017), self included: mean over N(i) + {i}, then W
+    sage = R.SAGEConv(fin, fout).double()
+    with torch.no_grad():
+        sage.weight.normal_(generator=g)
+        sage.bias.uniform_(-1, 1, generator=g)
+    Ah = A + torch.eye(n, dtype=F64)
+    want = (Ah.t() @ x) / Ah.sum(0).view(-1, 1) @ sage.weight.detach() + sage.bias.detach()
+    assert torch.allclose(sage(x, ei).detach(), want, rtol=1e-12, atol=1e-12)
+    # GIN (Xu et al. 2019): h((1 + eps) x_i + sum_{j in N(i)} x_j)
+    mlp = torch.nn.Sequential(torch.nn.Linear(fin, 6), torch.nn.ReLU(), torch.nn.Linear(6, fout)).double()
+    want = mlp(1.3 * x + A.t() @ x).detach()
+    assert torch.allclose(R.GINConv(mlp, eps=0.3)(x, ei).detach(), want, rtol=1e-12, atol=1e-12)
+    # GraphConv (Morris et al. 2019): Theta_1 x_i + sum_j e_ji Theta_2 x_j  (input loops kept)
+    w = torch.rand(ei.size(1), generator=g, dtype=F64)
+    gc = R.GraphConv(fin, fout).double()
+    with torch.no_grad():
+        gc.weight.normal_(generator=g)
+    want = _dense(ei, n, w).t() @ (x @ gc.weight.detach()) + gc.lin(x).detach()
+    assert torch.allclose(gc(x, ei, w).detach(), want, rtol=1e-12, atol=1e-12)
+    # AGNN (Thekumparampil et al. 2018): softmax_j(beta cos(x_i, x_j)) over N(i) + {i}
+    beta = 1.75          # exactly representable: the module holds beta in fp32 before .double()
+    xn = x / x.norm(dim=1, keepdim=True)
+    want = torch.zeros(n, fin, dtype=F64)
+    for i in range(n):
+        nb = [int(s) for s, d in nl.t().tolist() if d == i] + [i]
+        a = torch.softmax(torch.stack([beta * (xn[i] * xn[j]).sum() for j in nb]), 0)
+        want[i] = sum(al * x[j] for al, j in zip(a, nb))
+    assert torch.allclose(R.AGNNConv(beta).double()(x, ei).detach(), want, rtol=1e-12, atol=1e-12)
+
+
+def test_knn_radius_fps_oracles_against_a_kd_tree_and_the_greedy_definition():
+    from scipy.spatial import cKDTree
+    from oracle import ref_next as R
+    g = torch.Generator().manual_seed(11)
+    sizes = [40, 25, 33]
+    x = torch.rand(sum(sizes), 3, generator=g, dtype=F64)
+    batch = torch.cat([torch.full((m,), b) for b, m in enumerate(sizes)])
+    k, r = 5, 0.3
+    knn = R.knn_graph(x, k, batch)
+    rad = R.radius(x, x, r, batch, batch, max_num_neighbors=10 ** 6)
+    samp = R.fps(x, batch, ratio=0.25)
+    off = 0
+    picked = 0
+    for b, m in enumerate(sizes):
+        pts = x[off:off + m].numpy()
+        tree = cKDTree(pts)
+        _, nb = tree.query(pts, k=k + 1)                      # the point itself comes first
+        got = knn[0][knn[1] >= off][:m * k].view(m, k) - off if b == 0 else \
+            knn[0][(knn[1] >= off) & (knn[1] < off + m)].view(m, k) - off
+        assert np.array_equal(got.numpy(), nb[:, 1:])         # same neighbours, same distance order
+        balls = tree.query_ball_point(pts, r)
+        for q in range(m):
+            mine = rad[1][rad[0] == off + q] - off
+            assert mine.tolist() == sorted(balls[q])          # every point within r, ascending index
+        # farthest point sampling: ceil(0.25 m) picks, each the arg max of the distance to the picks
+        cnt = -(-m // 4)
+        sel = (samp[picked:picked + cnt] - off).tolist()
+        assert sel[0] == 0 and len(set(sel)) == cnt
+        for t in range(1, cnt):
+            dmin = ((pts[:, None] - pts[sel[:t]][None]) ** 2).sum(-1).min(1)
+            assert sel[t] == int(dmin.argmax())
+        picked += cnt
+        off += m
+    assert picked == samp.numel()
