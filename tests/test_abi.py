@@ -53,3 +53,16 @@ def test_product_does_not_import_oracle():
                 txt = open(os.path.join(dp, f)).read()
                 assert 'oracle' not in txt.replace('the oracle', '').replace("oracle's", ''), \
                     '{} mentions oracle'.format(f)
+
+
+def test_integration_doc_lists_every_entry_point():
+    """INTEGRATION.md tells a maintainer of the reference what each entry point replaces: a new
+    declaration in the header without a line there is documentation drift."""
+    doc = open(os.path.join(ROOT, 'INTEGRATION.md')).read()
+    listed = set(re.findall(r'pygb_[a-z0-9_]+', doc))
+    for m in re.finditer(r'(pygb_[a-z0-9_]*)\{([^}]*)\}', doc):           # pygb_peer_{alloc,free,...}
+        listed.update(m.group(1) + part.strip() for part in m.group(2).split(','))
+    for m in re.finditer(r'(pygb_[a-z0-9_]+)\(_([a-z0-9_]+)\)', doc):     # pygb_edge_softmax(_backward)
+        listed.add(m.group(1) + '_' + m.group(2))
+    missing = [n for n in _declared() if n not in listed]
+    assert not missing, missing
