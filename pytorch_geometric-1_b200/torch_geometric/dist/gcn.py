@@ -1,4 +1,4 @@
-"""Destination-partitioned GCN forward.
+"""Destination-partitioned GCN forward and backward.
 
 Rank ``p`` owns the node range ``[lo, hi)``: its rows of the features, its rows of
 every layer's output and the in-edges of those nodes.  Per layer the source
@@ -13,7 +13,7 @@ renumbering, exchange, layer order) is testable on CPU with ``gloo``.
 """
 import torch
 
-from .halo import HaloExchange
+from .halo import AllGatherRows, HaloExchange
 from .partition import PartitionPlan, balanced_bounds
 
 
@@ -65,6 +65,16 @@ def dist_gcn_layer(graph, x_local, weight, bias=None, aggregate=_native_aggregat
     ``[n_local, out]``.  Exchanges at ``min(in, out)`` channels."""
     fin, fout = weight.shape
     vec = 16 // x_local.element_size()
+    if torch.is_grad_enabled() and (x_local.requires_grad or weight.requires_grad or
+                                    (bias is not None and bias.requires_grad)):
+        # training: the exchange is an autograd node (all-gather forward, reduce-scatter backward);
+        # nothing is written in place.  Weight gradients are per-rank partial sums: all-reduce them
+        # (``all_reduce_grads``) before the optimiser step, as with any data-parallel layer.
+        if fin < fout:
+            agg = aggregate(graph, AllGatherRows.apply(x_local, graph.halo), None)
+            return transform(agg, weight, bias)
+        y = transform(x_local, weight, None)
+        return aggregate(graph, AllGatherRows.apply(y, graph.halo), bias)
     if fin < fout and fin % vec == 0:
         full = graph.halo.all_gather(x_local)                 # [P*block, fin]
         agg = aggregate(graph, full, None)                    # (A X) rows of this rank
@@ -84,3 +94,13 @@ def dist_gcn_forward(graph, x_local, layers, activation=torch.relu, aggregate=_n
         if k + 1 < len(layers):
             h = activation(h)
     return h
+
+
+def all_reduce_grads(params, group=None):
+    """Sum the per-rank partial gradients of replicated parameters (call after ``backward()``)."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    for p in params:
+        if p.grad is not None:
+            dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=group)

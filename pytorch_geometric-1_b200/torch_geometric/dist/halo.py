@@ -67,3 +67,38 @@ class HaloExchange(object):
     def bytes_received(self, ld, itemsize):
         p = self.plan
         return (p.world_size - 1) * p.block * ld * itemsize
+
+
+    def reduce_scatter(self, g_full):
+        """Transpose of ``all_gather``: ``g_full [P*block, F]`` (every rank's gradient for ALL source
+        rows) -> the sum over ranks of the rows this rank owns, ``[block, F]``.  NCCL reduce-scatter;
+        gloo (CPU unit tests) has none, so there it is an all-reduce and a slice."""
+        plan = self.plan
+        r0 = plan.rank * plan.block
+        if plan.world_size == 1:
+            return g_full[r0:r0 + plan.block]
+        g_full = g_full.contiguous()
+        if g_full.is_cuda:
+            out = torch.empty((plan.block, g_full.size(1)), dtype=g_full.dtype, device=g_full.device)
+            dist.reduce_scatter_tensor(out, g_full, op=dist.ReduceOp.SUM, group=self.group)
+            return out
+        g_full = g_full.clone()
+        dist.all_reduce(g_full, op=dist.ReduceOp.SUM, group=self.group)
+        return g_full[r0:r0 + plan.block]
+
+
+class AllGatherRows(torch.autograd.Function):
+    """``halo.all_gather`` with its transpose as the backward (training on the partitioned graph):
+    forward gathers the rank blocks ``[n_local, F] -> [P*block, F]``, backward reduce-scatters the
+    gradient of the gathered matrix back to the owners of the rows.  The output is a copy — the
+    gather buffer is reused by the next layer of the same width, autograd must own what it saved."""
+
+    @staticmethod
+    def forward(ctx, x_local, halo):
+        ctx.halo = halo
+        ctx.n_local = x_local.size(0)
+        return halo.all_gather(x_local).clone()
+
+    @staticmethod
+    def backward(ctx, g_full):
+        return ctx.halo.reduce_scatter(g_full)[:ctx.n_local], None

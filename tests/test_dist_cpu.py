@@ -102,6 +102,80 @@ def test_dist_gcn_two_ranks_gloo():
     assert nbytes > 0
 
 
+def _train_worker(rank, world, port, q):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from torch_geometric.dist import DistGraph, all_reduce_grads, dist_gcn_forward
+        torch.manual_seed(0)
+        n = 257
+        ei = random_graph(n, n, 3000, 6)
+        ei[1, :500] = 11                                  # a hub target
+        x = torch.randn(n, 8, dtype=torch.float64)
+        dims = [(8, 16), (16, 16), (16, 5)]               # aggregate-first, transform-first, narrow
+        layers = [((torch.randn(a, b, dtype=torch.float64) / a ** 0.5).requires_grad_(True),
+                   torch.randn(b, dtype=torch.float64).requires_grad_(True)) for a, b in dims]
+        coef = torch.randn(n, 5, dtype=torch.float64)     # loss = <out, coef>: a distinct weight per element
+        ei2, norm = O.gcn_norm(ei, n, dtype=torch.float64)
+        g = DistGraph(ei2, norm, n, rank, world, build_adj=False)
+        x_loc = g.local_rows(x).clone().requires_grad_(True)
+        # x * sigmoid(x): smooth, so the comparison has no activation kinks
+        out_local = dist_gcn_forward(g, x_loc, layers, activation=lambda t: t * torch.sigmoid(t),
+                                     aggregate=_oracle_aggregate, transform=_cpu_transform)
+        loss = (out_local * g.local_rows(coef)).sum()
+        loss.backward()
+        all_reduce_grads([p for wb in layers for p in wb])
+        total = loss.detach().clone()
+        dist.all_reduce(total)
+        gx = torch.zeros(g.plan.block, 8, dtype=torch.float64)
+        gx[:g.plan.n_local] = x_loc.grad
+        parts = [torch.zeros_like(gx) for _ in range(world)]
+        dist.all_gather(parts, gx)
+        if rank == 0:
+            got_gx = torch.cat([parts[p][:g.plan.bounds[p + 1] - g.plan.bounds[p]] for p in range(world)])
+            xr = x.clone().requires_grad_(True)
+            ref_layers = [(w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True))
+                          for w, b in layers]
+            h = xr
+            for k, (w, b) in enumerate(ref_layers):
+                h = O.scatter_('add', norm.view(-1, 1) * (h @ w)[ei2[0]], ei2[1], 0, n) + b
+                if k + 1 < len(ref_layers):
+                    h = h * torch.sigmoid(h)
+            ref_loss = (h * coef).sum()
+            ref_loss.backward()
+            errs = [abs(total.item() - ref_loss.item()) / abs(ref_loss.item()),
+                    ((got_gx - xr.grad).abs().max() / xr.grad.abs().max()).item()]
+            for (w, b), (rw, rb) in zip(layers, ref_layers):
+                errs.append(((w.grad - rw.grad).abs().max() / rw.grad.abs().max()).item())
+                errs.append(((b.grad - rb.grad).abs().max() / rb.grad.abs().max()).item())
+            q.put(('ok', max(errs)))
+    except Exception as e:  # pragma: no cover
+        q.put(('error', repr(e)))
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 3])
+def test_dist_gcn_training_step_gloo(world):
+    """Forward + backward on the destination-partitioned graph: the exchange is an autograd node
+    (all-gather forward, reduce-scatter backward), weight gradients are all-reduced; loss, d x and
+    every d W / d b equal the single-process autograd of the oracle (fp64)."""
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_train_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    status, err = q.get(timeout=10)
+    assert status == 'ok', err
+    assert err <= 1e-10, err
+
+
 def test_partition_plan_properties():
     from torch_geometric.dist import PartitionPlan, balanced_bounds
     deg = torch.tensor([0, 5, 1, 1, 1, 100, 1, 1, 0, 0, 3])
